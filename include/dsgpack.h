@@ -1,0 +1,193 @@
+/*
+ * dsgpack.h -- C ABI of libdsgpack.so: B200-native tar+gzip packing for DevSpace's upstream sync /
+ * kaniko build-context path.
+ *
+ * Drop-in boundary: the Go seam that stays is
+ *     func writeTar(files []*fileInformation, config *SyncConfig) (string, map[string]*fileInformation, error)
+ *                                                     /root/reference/pkg/devspace/sync/tar.go:146
+ * The Go side keeps the walk, exclude matching, os.Stat, the fileMap lookups and reading file bytes;
+ * what crosses this ABI is the list of tar headers it would have handed to tw.WriteHeader
+ * (tar.go:253,294) as POD `dsg_entry` records, plus the payload bytes it would have io.Copy'd
+ * (tar.go:298) in one arena. What comes back is the byte stream that gzip.NewWriter(f) (tar.go:156)
+ * would have received: a standard gzip file whose decompressed content is bit-identical to the
+ * archive/tar stream. INTEGRATION.md shows the cgo stub.
+ *
+ * Conventions: every function returns 0 (DSG_OK) or a negative dsg_status; no torch / C++ types;
+ * all pointers are plain host pointers unless the parameter name starts with `d_` (device pointer on
+ * the context's device). A context serves one caller at a time (SURVEY.md 8b "Threading").
+ * There is NO CPU fallback: without a usable CUDA device every compute entry point fails with
+ * DSG_E_CUDA.
+ */
+#ifndef DSGPACK_H
+#define DSGPACK_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DSG_ABI_VERSION 1
+
+typedef enum dsg_status {
+  DSG_OK = 0,
+  DSG_E_ARG = -1,        /* NULL / inconsistent arguments                                          */
+  DSG_E_CUDA = -2,       /* CUDA runtime error; text via dsg_last_error()                           */
+  DSG_E_HEADER = -3,     /* archive/tar would return ErrHeader / ErrFieldTooLong for some entry     */
+  DSG_E_TYPEFLAG = -4,   /* typeflag other than '0' / '5' (tar.go only emits files and empty dirs)  */
+  DSG_E_CAPACITY = -5,   /* caller's output buffer too small; required size in *out_len             */
+  DSG_E_UNCLEAN_NAME = -6, /* a PAX entry's name is not path.Clean()ed (tar.go names always are)    */
+  DSG_E_NOMEM = -7,      /* device / pinned allocation failed                                       */
+  DSG_E_RANGE = -8       /* payload range outside the arena                                         */
+} dsg_status;
+
+/*
+ * One tar.Header as tarFile / tarFolder build it before tw.WriteHeader:
+ *   tar.FileInfoHeader(stat) (tar.go:242,280) -> hdr.Name = relative path (tar.go:243,284)
+ *   -> Mode/Uid/Gid <- RemoteMode/RemoteUID/RemoteGID when the path is indexed (tar.go:246-250,287-291).
+ * 80 bytes, little endian, no pointers: the array is copied to the device as is.
+ * Strings live in a caller-provided string table (`strtab`); several entries may share one string.
+ */
+typedef struct dsg_entry {
+  uint64_t data_off;   /* payload offset in the arena (bytes); ignored when size == 0 or typeflag '5' */
+  int64_t size;        /* hdr.Size: stat.Size() for files, 0 for directories                         */
+  int64_t mtime_sec;   /* stat.ModTime() seconds; rounding to the nearest second (WriteHeader,        */
+  int64_t mode;        /*   Format unset) is done on the device. mode: perm|04000|02000|01000         */
+  int64_t uid;         /* hdr.Uid / hdr.Gid (Go int)                                                  */
+  int64_t gid;
+  uint32_t mtime_nsec; /* stat.ModTime() nanoseconds, 0..999999999                                    */
+  uint32_t name_off;   /* hdr.Name: bytes [name_off, name_off+name_len) of strtab                     */
+  uint32_t name_len;
+  uint32_t uname_off;  /* hdr.Uname (passwd lookup done by tar.FileInfoHeader on the host)            */
+  uint32_t gname_off;  /* hdr.Gname                                                                   */
+  uint16_t uname_len;
+  uint16_t gname_len;
+  uint8_t typeflag;    /* '0' regular file, '5' empty directory                                       */
+  uint8_t reserved[7]; /* must be zero                                                                */
+} dsg_entry;
+
+typedef struct dsg_ctx dsg_ctx; /* opaque */
+
+/* Compression level semantics follow compress/gzip: the reference hard-wires DefaultCompression
+ * (gzip.NewWriter, tar.go:156). DSG_LEVEL_STORED exists for incompressible inputs and tests. */
+#define DSG_LEVEL_STORED 0
+#define DSG_LEVEL_DEFAULT 6
+
+typedef struct dsg_opts {
+  uint32_t struct_size;    /* sizeof(dsg_opts), for forward compatibility                           */
+  int32_t level;           /* DSG_LEVEL_DEFAULT or DSG_LEVEL_STORED                                  */
+  uint64_t segment_bytes;  /* tar-stream bytes per pipeline segment (0 = default 256 MiB)            */
+  uint32_t flags;          /* DSG_F_*                                                                */
+  uint32_t reserved;
+} dsg_opts;
+
+#define DSG_F_NO_TRAILER 1u /* omit the 1024-byte tar trailer: for every shard but the last */
+
+/* Per-call timing and size counters (bench.py reads them; times are CUDA-event milliseconds). */
+typedef struct dsg_stats {
+  uint64_t entries;        /* N                                                                      */
+  uint64_t payload_bytes;  /* P = sum of file sizes                                                  */
+  uint64_t tar_bytes;      /* T = tar stream length                                                  */
+  uint64_t out_bytes;      /* C = gzip bytes produced                                                */
+  uint64_t h2d_bytes;      /* bytes copied host -> device (manifest + arena)                         */
+  uint64_t d2h_bytes;      /* bytes copied device -> host                                            */
+  float ms_total;          /* first enqueue -> last byte landed / produced                           */
+  float ms_plan;           /* tar plan kernels (classify + scan)                                     */
+  float ms_tar;            /* header + payload layout kernels                                        */
+  float ms_deflate;        /* LZ77 + Huffman + bit-pack kernel(s)                                    */
+  float ms_crc;            /* CRC32 kernel + combine                                                 */
+  float ms_gather;         /* compaction of per-chunk outputs                                        */
+  uint32_t kernel_launches;/* kernels launched by this call                                          */
+  uint32_t segments;       /* pipeline segments processed                                            */
+  uint32_t crc32;          /* CRC32-IEEE of the tar stream (gzip trailer)                            */
+  uint32_t reserved;
+} dsg_stats;
+
+/* ---- context ------------------------------------------------------------------------------------ */
+
+/* Replaces: nothing in Go (gzip.NewWriter / tar.NewWriter carry the per-archive state, tar.go:156,159);
+ * here the context owns the device, streams and reusable device/pinned buffers. */
+int dsg_ctx_create(int device, const dsg_opts *opts, dsg_ctx **out);
+void dsg_ctx_destroy(dsg_ctx *ctx);
+const char *dsg_last_error(const dsg_ctx *ctx);   /* text of the last failure (CUDA error string etc.) */
+const char *dsg_strerror(int status);
+int dsg_abi_version(void);
+int dsg_device_count(void);                       /* 0 when no CUDA device is usable                   */
+
+/* Page-locked staging memory for the arena / output (the Go shim wraps it with unsafe.Slice; it stands
+ * where tarFile's io.Copy source buffer and the temp file's write buffer were, tar.go:147,298). */
+void *dsg_pinned_alloc(dsg_ctx *ctx, size_t bytes);
+void dsg_pinned_free(dsg_ctx *ctx, void *p);
+
+/* ---- host-side layout helpers (pure integer work on the manifest; no GPU) ------------------------- */
+
+/* Bytes tw.WriteHeader emits for one entry: 512, or 512 + pad512(PAX records) + 512.
+ * Same decision procedure as Header.allowedFormats in go1.11 archive/tar. */
+int dsg_entry_header_bytes(const dsg_entry *e, const char *strtab, size_t strtab_len, uint64_t *out);
+
+/* T: total tar stream length for the manifest, including the 1024-byte trailer (Writer.Close) unless
+ * flags has DSG_F_NO_TRAILER. */
+int dsg_tar_size(const dsg_entry *entries, size_t n, const char *strtab, size_t strtab_len, uint32_t flags,
+                 uint64_t *out);
+
+/* Upper bound of the gzip output for a tar stream of `tar_bytes` bytes (for sizing `out`). */
+uint64_t dsg_gzip_bound(uint64_t tar_bytes);
+
+/* Contiguous entry ranges balanced by tar-stream bytes for `nshards` GPUs:
+ * shard s owns entries [bounds[s], bounds[s+1]). `bounds` has nshards+1 slots. Files are never split. */
+int dsg_shard_bounds(const dsg_entry *entries, size_t n, const char *strtab, size_t strtab_len, int nshards,
+                     uint64_t *bounds);
+
+/* ---- the hot path ------------------------------------------------------------------------------- */
+
+/* Replaces the body of writeTar (tar.go:146-182) below the walk: tar.NewWriter(gzip.NewWriter(f)),
+ * WriteHeader + io.Copy per entry, tarWriter.Close, gw.Close. Host buffers in, host buffer out;
+ * copies are pipelined with the kernels per segment. `out` receives one complete gzip member.
+ * On DSG_E_CAPACITY *out_len holds the size that would have been needed. */
+int dsg_pack(dsg_ctx *ctx, const dsg_entry *entries, size_t n, const char *strtab, size_t strtab_len,
+             const uint8_t *arena, size_t arena_len, uint8_t *out, size_t out_cap, size_t *out_len);
+
+/* Same, without gzip: the uncompressed archive/tar stream (what tar.NewWriter(w) writes to w).
+ * Next-row use: the docker builder's uncompressed context (builder/docker/docker.go:94-97). */
+int dsg_pack_tar_only(dsg_ctx *ctx, const dsg_entry *entries, size_t n, const char *strtab, size_t strtab_len,
+                      const uint8_t *arena, size_t arena_len, uint8_t *out, size_t out_cap, size_t *out_len);
+
+/* Device-resident variant of dsg_pack for callers that already hold manifest + arena in HBM
+ * (bench.py's kernel-only number): every `d_` pointer is device memory on the context's device.
+ * *out_len is written on the host after the call's own synchronisation. */
+int dsg_pack_device(dsg_ctx *ctx, const dsg_entry *d_entries, size_t n, const char *d_strtab, size_t strtab_len,
+                    const uint8_t *d_arena, size_t arena_len, uint8_t *d_out, size_t out_cap, size_t *out_len);
+
+/* Counters of the most recent dsg_pack* call on this context. */
+int dsg_get_stats(const dsg_ctx *ctx, dsg_stats *out);
+
+/* ---- single stages, device pointers (parity tests drive each kernel alone) ----------------------- */
+
+/* archive/tar Writer: headers + payload layout + padding + trailer into d_tar[tar_cap]. */
+int dsg_dev_tar_build(dsg_ctx *ctx, const dsg_entry *d_entries, size_t n, const char *d_strtab, size_t strtab_len,
+                      const uint8_t *d_arena, size_t arena_len, uint32_t flags, uint8_t *d_tar, size_t tar_cap,
+                      uint64_t *tar_len);
+
+/* hash/crc32 ChecksumIEEE over d_buf[0,len) (gzip.Writer keeps it as z.digest). */
+int dsg_dev_crc32(dsg_ctx *ctx, const uint8_t *d_buf, size_t len, uint32_t *crc);
+
+/* compress/flate Writer at `level`: raw deflate stream (byte aligned, BFINAL set on the last block)
+ * of d_in[0,len) into d_out[out_cap]. */
+int dsg_dev_deflate(dsg_ctx *ctx, const uint8_t *d_in, size_t len, int level, uint8_t *d_out, size_t out_cap,
+                    size_t *out_len);
+
+/* compress/gzip Writer: header + deflate + CRC32 + ISIZE for an existing device buffer. */
+int dsg_dev_gzip(dsg_ctx *ctx, const uint8_t *d_in, size_t len, int level, uint8_t *d_out, size_t out_cap,
+                 size_t *out_len);
+
+/* Plain device memory helpers so that ctypes / cgo callers need no CUDA binding of their own. */
+void *dsg_dev_alloc(dsg_ctx *ctx, size_t bytes);
+void dsg_dev_free(dsg_ctx *ctx, void *d_ptr);
+int dsg_dev_upload(dsg_ctx *ctx, void *d_dst, const void *src, size_t bytes);
+int dsg_dev_download(dsg_ctx *ctx, void *dst, const void *d_src, size_t bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DSGPACK_H */
