@@ -1,0 +1,738 @@
+// dsgpack.cu -- host engine and C ABI of libdsgpack.so (include/dsgpack.h).
+//
+// Replaces the body of writeTar below the directory walk
+// (/root/reference/pkg/devspace/sync/tar.go:146-182: gzip.NewWriter -> tar.NewWriter -> per entry
+// WriteHeader + io.Copy -> tarWriter.Close -> gw.Close) with CUDA kernels for sm_100a.
+// No CPU fallback: every compute entry point needs a CUDA device and fails with DSG_E_CUDA otherwise.
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "crc32.cuh"
+#include "deflate_lz.cuh"
+#include "deflate_stored.cuh"
+#include "tar_kernels.cuh"
+
+using namespace dsg;
+
+namespace {
+
+struct DevBuf {
+  void *p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      e = cudaMalloc(&p, bytes + 256);
+      want = bytes + 256;
+    }
+    if (e == cudaSuccess) cap = want - 256;  // 256 bytes of slack behind every buffer (aligned over-reads)
+    return e;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+  template <typename T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+struct Timer {
+  cudaEvent_t a = nullptr, b = nullptr;
+  bool used = false;
+};
+
+enum { kTimPlan, kTimTar, kTimDeflate, kTimCrc, kTimGather, kTimTotal, kTimCount };
+
+}  // namespace
+
+struct dsg_ctx {
+  int device = 0;
+  dsg_opts opts{};
+  cudaStream_t stream = nullptr;
+  std::string err;
+  dsg_stats stats{};
+  std::mutex mu;
+  // constant tables
+  DevBuf crc_tab, crc_shift;
+  // plan
+  DevBuf ent_blocks, cta_sums, ent_off, scalars;  // scalars: [0] total_blocks u64, [1] payload u64, [2..] status, crc state
+  // staging of host inputs / outputs
+  DevBuf d_entries, d_strtab, d_arena, d_tar, d_out;
+  // crc
+  DevBuf crc_raw;
+  // deflate
+  DevBuf lz_scratch, chunk_sizes, chunk_offs;
+  Timer tim[kTimCount];
+  uint64_t *h_scalars = nullptr;  // pinned mirror of `scalars`
+  uint32_t launches = 0;
+  int sm_count = 148;
+};
+
+namespace {
+
+constexpr size_t kScalarWords = 16;  // u64 slots
+// slot layout inside `scalars` (u64 units)
+enum { kSTotalBlocks = 0, kSPayload = 1, kSStatus = 2 /* DevStatus, 8 bytes */, kSCrc = 3 /* 3 x u32 in 2 slots */,
+       kSDeflateBytes = 5, kSSpare = 6 };
+
+int fail(dsg_ctx *c, int code, const char *fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  if (c) c->err = buf;
+  return code;
+}
+
+#define CU(call)                                                                                         \
+  do {                                                                                                   \
+    cudaError_t e_ = (call);                                                                             \
+    if (e_ != cudaSuccess) {                                                                             \
+      cudaGetLastError();                                                                                \
+      return fail(ctx, e_ == cudaErrorMemoryAllocation ? DSG_E_NOMEM : DSG_E_CUDA, "%s: %s (%s:%d)", #call, \
+                  cudaGetErrorString(e_), __FILE__, __LINE__);                                           \
+    }                                                                                                    \
+  } while (0)
+
+#define LAUNCH_CHECK()                                                      \
+  do {                                                                      \
+    ctx->launches++;                                                        \
+    CU(cudaGetLastError());                                                 \
+  } while (0)
+
+int lz_ctx_init(dsg_ctx *ctx);
+int lz_deflate_run(dsg_ctx *ctx, const uint8_t *d_in, uint64_t len, uint8_t *d_out, uint64_t out_cap, uint64_t *out_len);
+
+void tic(dsg_ctx *ctx, int which) {
+  Timer &t = ctx->tim[which];
+  cudaEventRecord(t.a, ctx->stream);
+}
+void toc(dsg_ctx *ctx, int which) {
+  Timer &t = ctx->tim[which];
+  cudaEventRecord(t.b, ctx->stream);
+  t.used = true;
+}
+float elapsed(dsg_ctx *ctx, int which) {
+  Timer &t = ctx->tim[which];
+  if (!t.used) return 0.f;
+  float ms = 0.f;
+  if (cudaEventElapsedTime(&ms, t.a, t.b) != cudaSuccess) {
+    cudaGetLastError();
+    return 0.f;
+  }
+  return ms;
+}
+
+int begin_call(dsg_ctx *ctx) {
+  CU(cudaSetDevice(ctx->device));
+  ctx->launches = 0;
+  memset(&ctx->stats, 0, sizeof ctx->stats);
+  for (auto &t : ctx->tim) t.used = false;
+  ctx->err.clear();
+  return DSG_OK;
+}
+
+// ---- stage: archive/tar Writer ---------------------------------------------------------------------------
+
+// Runs the plan kernels and returns T (synchronises once to read it and the status word).
+int tar_plan(dsg_ctx *ctx, const dsg_entry *d_entries, uint32_t n, const char *d_strtab, uint64_t strtab_len,
+             uint64_t arena_len, uint32_t flags, uint64_t *tar_len, uint64_t *payload) {
+  const uint32_t ncta = (n + kPlanThreads - 1) / kPlanThreads;
+  CU(ctx->ent_blocks.ensure(sizeof(uint64_t) * (size_t)(n + 1)));
+  CU(ctx->cta_sums.ensure(sizeof(uint64_t) * (size_t)(ncta + 1)));
+  CU(ctx->ent_off.ensure(sizeof(uint64_t) * (size_t)(n + 1)));
+  uint64_t *sc = ctx->scalars.as<uint64_t>();
+  memset(ctx->h_scalars, 0, sizeof(uint64_t) * kScalarWords);
+  DevStatus st0{0, 0xffffffffu};
+  memcpy(&ctx->h_scalars[kSStatus], &st0, sizeof st0);
+  CU(cudaMemcpyAsync(sc, ctx->h_scalars, sizeof(uint64_t) * kScalarWords, cudaMemcpyHostToDevice, ctx->stream));
+  tic(ctx, kTimPlan);
+  if (n) {
+    tar_classify_kernel<<<ncta, kPlanThreads, 0, ctx->stream>>>(
+        d_entries, n, d_strtab, strtab_len, arena_len, ctx->ent_blocks.as<uint64_t>(), ctx->cta_sums.as<uint64_t>(),
+        reinterpret_cast<unsigned long long *>(sc + kSPayload), reinterpret_cast<DevStatus *>(sc + kSStatus));
+    LAUNCH_CHECK();
+    tar_scan_partials<<<1, 1024, 0, ctx->stream>>>(ctx->cta_sums.as<uint64_t>(), ncta, sc + kSTotalBlocks);
+    LAUNCH_CHECK();
+    tar_offsets_kernel<<<ncta, kPlanThreads, 0, ctx->stream>>>(ctx->ent_blocks.as<uint64_t>(), n,
+                                                              ctx->cta_sums.as<uint64_t>(), ctx->ent_off.as<uint64_t>());
+    LAUNCH_CHECK();
+  } else {
+    CU(cudaMemsetAsync(ctx->ent_off.p, 0, sizeof(uint64_t), ctx->stream));
+  }
+  toc(ctx, kTimPlan);
+  CU(cudaMemcpyAsync(ctx->h_scalars, sc, sizeof(uint64_t) * kScalarWords, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  DevStatus st;
+  memcpy(&st, &ctx->h_scalars[kSStatus], sizeof st);
+  if (st.code != 0) return fail(ctx, st.code, "entry %u: %s", st.entry, dsg_strerror(st.code));
+  *tar_len = ctx->h_scalars[kSTotalBlocks] * kBlock + ((flags & DSG_F_NO_TRAILER) ? 0 : 2 * kBlock);
+  if (payload) *payload = ctx->h_scalars[kSPayload];
+  return DSG_OK;
+}
+
+// Writes stream bytes [lo, hi) (multiples of 512) to d_dst; d_arena holds arena bytes from arena_base on.
+int tar_layout(dsg_ctx *ctx, const dsg_entry *d_entries, uint32_t n, const char *d_strtab, const uint8_t *d_arena,
+               uint64_t arena_base, uint8_t *d_dst, uint64_t lo, uint64_t hi) {
+  if (hi <= lo) return DSG_OK;
+  const uint64_t tiles = (hi - lo + kTileBytes - 1) / kTileBytes;
+  uint64_t *sc = ctx->scalars.as<uint64_t>();
+  tar_layout_kernel<<<(unsigned)tiles, kLayoutThreads, 0, ctx->stream>>>(
+      d_entries, n, d_strtab, ctx->ent_off.as<uint64_t>(), d_arena, arena_base, d_dst, lo, hi,
+      reinterpret_cast<DevStatus *>(sc + kSStatus));
+  LAUNCH_CHECK();
+  return DSG_OK;
+}
+
+int check_status(dsg_ctx *ctx) {
+  uint64_t *sc = ctx->scalars.as<uint64_t>();
+  CU(cudaMemcpyAsync(ctx->h_scalars, sc, sizeof(uint64_t) * kScalarWords, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  DevStatus st;
+  memcpy(&st, &ctx->h_scalars[kSStatus], sizeof st);
+  if (st.code != 0) return fail(ctx, st.code, "entry %u: %s", st.entry, dsg_strerror(st.code));
+  return DSG_OK;
+}
+
+// ---- stage: CRC32 -------------------------------------------------------------------------------------------
+
+// Folds d_buf[0,len) into the running CRC state kept in scalars[kSCrc..] (device resident, no sync).
+int crc_update(dsg_ctx *ctx, const uint8_t *d_buf, uint64_t len) {
+  if (len == 0) return DSG_OK;
+  uint32_t head = (uint32_t)((16 - ((uintptr_t)d_buf & 15)) & 15);
+  if (head > len) head = (uint32_t)len;
+  const uint64_t body = (len - head) & ~uint64_t(15);
+  const uint32_t tail = (uint32_t)(len - head - body);
+  const uint32_t ntiles = (uint32_t)((body + kCrcTileBytes - 1) / kCrcTileBytes);
+  CU(ctx->crc_raw.ensure(sizeof(uint32_t) * (size_t)(ntiles + 1)));
+  uint32_t *state = reinterpret_cast<uint32_t *>(ctx->scalars.as<uint64_t>() + kSCrc);
+  if (ntiles) {
+    crc_tiles_kernel<<<ntiles, kCrcThreads, 0, ctx->stream>>>(reinterpret_cast<const uint4 *>(d_buf + head), body / 16,
+                                                            ctx->crc_tab.as<uint32_t>(), ctx->crc_shift.as<uint32_t>(),
+                                                            ctx->crc_raw.as<uint32_t>());
+    LAUNCH_CHECK();
+  }
+  crc_join_kernel<<<1, 256, 0, ctx->stream>>>(ctx->crc_raw.as<uint32_t>(), ntiles, body, d_buf, head,
+                                              d_buf + head + body, tail, state);
+  LAUNCH_CHECK();
+  return DSG_OK;
+}
+
+int crc_reset(dsg_ctx *ctx) {
+  CU(cudaMemsetAsync(ctx->scalars.as<uint64_t>() + kSCrc, 0, 2 * sizeof(uint64_t), ctx->stream));
+  return DSG_OK;
+}
+
+// ---- stage: deflate -----------------------------------------------------------------------------------------
+
+__global__ void gzip_frame_kernel(uint8_t *out, const uint64_t *deflate_bytes, const uint32_t *crc_state) {
+  // compress/gzip Writer: 1f 8b 08 00 | mtime 0 | XFL 0 | OS ff ... CRC32 LE, ISIZE LE
+  if (threadIdx.x == 0) {
+    const uint8_t hdr[10] = {0x1f, 0x8b, 0x08, 0, 0, 0, 0, 0, 0, 0xff};
+    for (int i = 0; i < 10; i++) out[i] = hdr[i];
+    uint8_t *t = out + 10 + *deflate_bytes;
+    const uint32_t crc = crc_state[0], isize = crc_state[1];
+    for (int i = 0; i < 4; i++) t[i] = (uint8_t)(crc >> (8 * i));
+    for (int i = 0; i < 4; i++) t[4 + i] = (uint8_t)(isize >> (8 * i));
+  }
+}
+
+__global__ void set_u64_kernel(uint64_t *p, uint64_t v) { *p = v; }
+
+// Raw deflate of d_in[0,len) to d_out (capacity out_cap). Size lands in scalars[kSDeflateBytes] on the
+// device and, via *out_len (after a sync), on the host.
+int deflate_run(dsg_ctx *ctx, const uint8_t *d_in, uint64_t len, int level, uint8_t *d_out, uint64_t out_cap,
+                uint64_t *out_len) {
+  uint64_t *sc = ctx->scalars.as<uint64_t>();
+  tic(ctx, kTimDeflate);
+  if (level == DSG_LEVEL_STORED) {
+    const uint64_t need = stored_deflate_size(len);
+    if (need > out_cap) {
+      *out_len = need;
+      return fail(ctx, DSG_E_CAPACITY, "deflate output needs %llu bytes, capacity %llu", (unsigned long long)need,
+                  (unsigned long long)out_cap);
+    }
+    const uint64_t nblocks = (len + kStoredMax - 1) / kStoredMax;
+    deflate_stored_kernel<<<(unsigned)std::max<uint64_t>(nblocks, 1), kStoredThreads, 0, ctx->stream>>>(d_in, len, d_out, 1);
+    LAUNCH_CHECK();
+    set_u64_kernel<<<1, 1, 0, ctx->stream>>>(sc + kSDeflateBytes, need);
+    LAUNCH_CHECK();
+    toc(ctx, kTimDeflate);
+    *out_len = need;
+    return DSG_OK;
+  }
+  int rc = lz_deflate_run(ctx, d_in, len, d_out, out_cap, out_len);
+  toc(ctx, kTimDeflate);
+  return rc;
+}
+
+// ---- LZ77 + Huffman path (level 6) -------------------------------------------------------------------------
+
+int lz_ctx_init(dsg_ctx *ctx) {
+  (void)ctx;
+  return DSG_OK;
+}
+
+int lz_deflate_run(dsg_ctx *ctx, const uint8_t *d_in, uint64_t len, uint8_t *d_out, uint64_t out_cap,
+                   uint64_t *out_len) {
+  (void)d_in; (void)len; (void)d_out; (void)out_cap; (void)out_len;
+  return fail(ctx, DSG_E_ARG, "level 6 kernels are not part of this build yet");
+}
+
+}  // namespace
+
+// =================================================================================================================
+// C ABI
+// =================================================================================================================
+
+extern "C" {
+
+int dsg_abi_version(void) { return DSG_ABI_VERSION; }
+
+const char *dsg_strerror(int status) {
+  switch (status) {
+    case DSG_OK: return "ok";
+    case DSG_E_ARG: return "invalid argument";
+    case DSG_E_CUDA: return "CUDA error";
+    case DSG_E_HEADER: return "archive/tar: header field cannot be encoded";
+    case DSG_E_TYPEFLAG: return "typeflag is neither '0' nor '5'";
+    case DSG_E_CAPACITY: return "output buffer too small";
+    case DSG_E_UNCLEAN_NAME: return "PAX entry name is not path.Clean()ed";
+    case DSG_E_NOMEM: return "out of device or pinned memory";
+    case DSG_E_RANGE: return "payload range outside the arena";
+    default: return "unknown status";
+  }
+}
+
+int dsg_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+const char *dsg_last_error(const dsg_ctx *ctx) { return ctx ? ctx->err.c_str() : "no context"; }
+
+int dsg_ctx_create(int device, const dsg_opts *opts, dsg_ctx **out) {
+  if (!out) return DSG_E_ARG;
+  *out = nullptr;
+  int ndev = dsg_device_count();
+  if (ndev <= 0 || device < 0 || device >= ndev) return DSG_E_CUDA;  // no CPU fallback
+  dsg_ctx *ctx = new dsg_ctx();
+  ctx->device = device;
+  ctx->opts.struct_size = sizeof(dsg_opts);
+  ctx->opts.level = DSG_LEVEL_DEFAULT;
+  ctx->opts.segment_bytes = 0;
+  if (opts) {
+    size_t k = std::min<size_t>(opts->struct_size, sizeof(dsg_opts));
+    memcpy(&ctx->opts, opts, k);
+    ctx->opts.struct_size = sizeof(dsg_opts);
+  }
+  if (ctx->opts.segment_bytes == 0) ctx->opts.segment_bytes = 256ull << 20;
+  auto bail = [&](cudaError_t e, const char *what) {
+    fprintf(stderr, "dsg_ctx_create: %s: %s\n", what, cudaGetErrorString(e));
+    cudaGetLastError();
+    dsg_ctx_destroy(ctx);
+    return DSG_E_CUDA;
+  };
+  cudaError_t e;
+  if ((e = cudaSetDevice(device)) != cudaSuccess) return bail(e, "cudaSetDevice");
+  cudaDeviceProp prop;
+  if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return bail(e, "cudaGetDeviceProperties");
+  ctx->sm_count = prop.multiProcessorCount;
+  if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "stream");
+  for (auto &t : ctx->tim) {
+    if ((e = cudaEventCreate(&t.a)) != cudaSuccess) return bail(e, "event");
+    if ((e = cudaEventCreate(&t.b)) != cudaSuccess) return bail(e, "event");
+  }
+  if ((e = cudaMallocHost(reinterpret_cast<void **>(&ctx->h_scalars), sizeof(uint64_t) * kScalarWords)) != cudaSuccess)
+    return bail(e, "cudaMallocHost");
+  if ((e = ctx->scalars.ensure(sizeof(uint64_t) * kScalarWords)) != cudaSuccess) return bail(e, "scalars");
+  // CRC tables: built once on the host (2 x 5120 table entries), resident for the context's lifetime
+  std::vector<uint32_t> tab(kCrcTables * 256), shift(kCrcShiftEntries);
+  crc_build_tables(tab.data(), shift.data(), (uint64_t)kCrcThreads * 16);
+  if ((e = ctx->crc_tab.ensure(tab.size() * 4)) != cudaSuccess) return bail(e, "crc_tab");
+  if ((e = ctx->crc_shift.ensure(shift.size() * 4)) != cudaSuccess) return bail(e, "crc_shift");
+  if ((e = cudaMemcpy(ctx->crc_tab.p, tab.data(), tab.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess)
+    return bail(e, "crc_tab upload");
+  if ((e = cudaMemcpy(ctx->crc_shift.p, shift.data(), shift.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess)
+    return bail(e, "crc_shift upload");
+  int rc = lz_ctx_init(ctx);
+  if (rc != DSG_OK) {
+    fprintf(stderr, "dsg_ctx_create: %s\n", ctx->err.c_str());
+    dsg_ctx_destroy(ctx);
+    return rc;
+  }
+  *out = ctx;
+  return DSG_OK;
+}
+
+void dsg_ctx_destroy(dsg_ctx *ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  for (DevBuf *b : {&ctx->crc_tab, &ctx->crc_shift, &ctx->ent_blocks, &ctx->cta_sums, &ctx->ent_off, &ctx->scalars,
+                    &ctx->d_entries, &ctx->d_strtab, &ctx->d_arena, &ctx->d_tar, &ctx->d_out, &ctx->crc_raw,
+                    &ctx->lz_scratch, &ctx->chunk_sizes, &ctx->chunk_offs})
+    b->release();
+  for (auto &t : ctx->tim) {
+    if (t.a) cudaEventDestroy(t.a);
+    if (t.b) cudaEventDestroy(t.b);
+  }
+  if (ctx->h_scalars) cudaFreeHost(ctx->h_scalars);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  cudaGetLastError();
+  delete ctx;
+}
+
+void *dsg_pinned_alloc(dsg_ctx *ctx, size_t bytes) {
+  if (!ctx) return nullptr;
+  cudaSetDevice(ctx->device);
+  void *p = nullptr;
+  if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  return p;
+}
+void dsg_pinned_free(dsg_ctx *ctx, void *p) {
+  if (!ctx || !p) return;
+  cudaSetDevice(ctx->device);
+  cudaFreeHost(p);
+}
+
+void *dsg_dev_alloc(dsg_ctx *ctx, size_t bytes) {
+  if (!ctx) return nullptr;
+  cudaSetDevice(ctx->device);
+  void *p = nullptr;
+  if (cudaMalloc(&p, bytes + 256) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  return p;
+}
+void dsg_dev_free(dsg_ctx *ctx, void *p) {
+  if (!ctx || !p) return;
+  cudaSetDevice(ctx->device);
+  cudaFree(p);
+}
+int dsg_dev_upload(dsg_ctx *ctx, void *d_dst, const void *src, size_t bytes) {
+  if (!ctx) return DSG_E_ARG;
+  CU(cudaSetDevice(ctx->device));
+  CU(cudaMemcpyAsync(d_dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return DSG_OK;
+}
+int dsg_dev_download(dsg_ctx *ctx, void *dst, const void *d_src, size_t bytes) {
+  if (!ctx) return DSG_E_ARG;
+  CU(cudaSetDevice(ctx->device));
+  CU(cudaMemcpyAsync(dst, d_src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return DSG_OK;
+}
+
+// ---- host-side layout helpers ---------------------------------------------------------------------------------
+
+int dsg_entry_header_bytes(const dsg_entry *e, const char *strtab, size_t strtab_len, uint64_t *out) {
+  if (!e || !strtab || !out) return DSG_E_ARG;
+  HdrPlan p;
+  int rc = classify_entry(*e, strtab, strtab_len, p);
+  if (rc != DSG_OK) return rc;
+  *out = p.hdr_bytes;
+  return DSG_OK;
+}
+
+int dsg_tar_size(const dsg_entry *entries, size_t n, const char *strtab, size_t strtab_len, uint32_t flags,
+                 uint64_t *out) {
+  if ((!entries && n) || !strtab || !out) return DSG_E_ARG;
+  uint64_t t = 0;
+  for (size_t i = 0; i < n; i++) {
+    HdrPlan p;
+    int rc = classify_entry(entries[i], strtab, strtab_len, p);
+    if (rc != DSG_OK) return rc;
+    t += p.hdr_bytes + entry_payload_padded(entries[i]);
+  }
+  *out = t + ((flags & DSG_F_NO_TRAILER) ? 0 : 2 * kBlock);
+  return DSG_OK;
+}
+
+uint64_t dsg_gzip_bound(uint64_t tar_bytes) { return 18 + lz_deflate_bound(tar_bytes); }
+
+int dsg_shard_bounds(const dsg_entry *entries, size_t n, const char *strtab, size_t strtab_len, int nshards,
+                     uint64_t *bounds) {
+  if ((!entries && n) || !strtab || !bounds || nshards <= 0) return DSG_E_ARG;
+  std::vector<uint64_t> pre(n + 1, 0);
+  for (size_t i = 0; i < n; i++) {
+    HdrPlan p;
+    int rc = classify_entry(entries[i], strtab, strtab_len, p);
+    if (rc != DSG_OK) return rc;
+    pre[i + 1] = pre[i] + p.hdr_bytes + entry_payload_padded(entries[i]);
+  }
+  const uint64_t total = pre[n];
+  bounds[0] = 0;
+  for (int s = 1; s < nshards; s++) {
+    // first entry whose start offset reaches s/nshards of the stream; files are never split
+    const uint64_t target = (uint64_t)(((unsigned __int128)total * (unsigned)s) / (unsigned)nshards);
+    size_t k = std::lower_bound(pre.begin(), pre.end(), target) - pre.begin();
+    if (k > n) k = n;
+    if (k < bounds[s - 1]) k = bounds[s - 1];
+    bounds[s] = k;
+  }
+  bounds[nshards] = n;
+  return DSG_OK;
+}
+
+// ---- single stages ------------------------------------------------------------------------------------------
+
+int dsg_dev_tar_build(dsg_ctx *ctx, const dsg_entry *d_entries, size_t n, const char *d_strtab, size_t strtab_len,
+                      const uint8_t *d_arena, size_t arena_len, uint32_t flags, uint8_t *d_tar, size_t tar_cap,
+                      uint64_t *tar_len) {
+  if (!ctx || !tar_len || (n && (!d_entries || !d_strtab)) || n > 0xfffffff0ull) return DSG_E_ARG;
+  std::lock_guard<std::mutex> g(ctx->mu);
+  int rc = begin_call(ctx);
+  if (rc) return rc;
+  uint64_t T = 0, P = 0;
+  rc = tar_plan(ctx, d_entries, (uint32_t)n, d_strtab, strtab_len, arena_len, flags, &T, &P);
+  if (rc) return rc;
+  *tar_len = T;
+  if (T > tar_cap) return fail(ctx, DSG_E_CAPACITY, "tar stream needs %llu bytes", (unsigned long long)T);
+  tic(ctx, kTimTar);
+  rc = tar_layout(ctx, d_entries, (uint32_t)n, d_strtab, d_arena, 0, d_tar, 0, T);
+  if (rc) return rc;
+  toc(ctx, kTimTar);
+  rc = check_status(ctx);
+  ctx->stats.entries = n;
+  ctx->stats.payload_bytes = P;
+  ctx->stats.tar_bytes = T;
+  ctx->stats.ms_plan = elapsed(ctx, kTimPlan);
+  ctx->stats.ms_tar = elapsed(ctx, kTimTar);
+  ctx->stats.kernel_launches = ctx->launches;
+  return rc;
+}
+
+int dsg_dev_crc32(dsg_ctx *ctx, const uint8_t *d_buf, size_t len, uint32_t *crc) {
+  if (!ctx || !crc || (len && !d_buf)) return DSG_E_ARG;
+  std::lock_guard<std::mutex> g(ctx->mu);
+  int rc = begin_call(ctx);
+  if (rc) return rc;
+  if ((rc = crc_reset(ctx))) return rc;
+  tic(ctx, kTimCrc);
+  if ((rc = crc_update(ctx, d_buf, len))) return rc;
+  toc(ctx, kTimCrc);
+  CU(cudaMemcpyAsync(ctx->h_scalars, ctx->scalars.p, sizeof(uint64_t) * kScalarWords, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  *crc = (uint32_t)ctx->h_scalars[kSCrc];
+  ctx->stats.ms_crc = elapsed(ctx, kTimCrc);
+  ctx->stats.crc32 = *crc;
+  ctx->stats.kernel_launches = ctx->launches;
+  return DSG_OK;
+}
+
+int dsg_dev_deflate(dsg_ctx *ctx, const uint8_t *d_in, size_t len, int level, uint8_t *d_out, size_t out_cap,
+                    size_t *out_len) {
+  if (!ctx || !out_len || !d_out || (len && !d_in)) return DSG_E_ARG;
+  if (level != DSG_LEVEL_STORED && level != DSG_LEVEL_DEFAULT) return fail(ctx, DSG_E_ARG, "level must be 0 or 6");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  int rc = begin_call(ctx);
+  if (rc) return rc;
+  uint64_t n = 0;
+  rc = deflate_run(ctx, d_in, len, level, d_out, out_cap, &n);
+  *out_len = (size_t)n;
+  if (rc) return rc;
+  CU(cudaStreamSynchronize(ctx->stream));
+  if (level != DSG_LEVEL_STORED) {
+    CU(cudaMemcpy(ctx->h_scalars, ctx->scalars.p, sizeof(uint64_t) * kScalarWords, cudaMemcpyDeviceToHost));
+    n = ctx->h_scalars[kSDeflateBytes];
+    *out_len = (size_t)n;
+  }
+  ctx->stats.tar_bytes = len;
+  ctx->stats.out_bytes = n;
+  ctx->stats.ms_deflate = elapsed(ctx, kTimDeflate);
+  ctx->stats.ms_gather = elapsed(ctx, kTimGather);
+  ctx->stats.kernel_launches = ctx->launches;
+  return DSG_OK;
+}
+
+// gzip member around an existing device buffer: header | deflate | crc32 | isize
+static int gzip_device(dsg_ctx *ctx, const uint8_t *d_in, uint64_t len, int level, uint8_t *d_out, uint64_t out_cap,
+                       uint64_t *out_len) {
+  if (out_cap < 18) {
+    *out_len = dsg_gzip_bound(len);
+    return fail(ctx, DSG_E_CAPACITY, "gzip output needs at least 18 bytes");
+  }
+  int rc;
+  if ((rc = crc_reset(ctx))) return rc;
+  tic(ctx, kTimCrc);
+  if ((rc = crc_update(ctx, d_in, len))) return rc;
+  toc(ctx, kTimCrc);
+  uint64_t dn = 0;
+  rc = deflate_run(ctx, d_in, len, level, d_out + 10, out_cap - 18, &dn);
+  if (rc) {
+    *out_len = dn + 18;
+    return rc;
+  }
+  uint64_t *sc = ctx->scalars.as<uint64_t>();
+  gzip_frame_kernel<<<1, 32, 0, ctx->stream>>>(d_out, sc + kSDeflateBytes, reinterpret_cast<uint32_t *>(sc + kSCrc));
+  LAUNCH_CHECK();
+  CU(cudaMemcpyAsync(ctx->h_scalars, sc, sizeof(uint64_t) * kScalarWords, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  *out_len = ctx->h_scalars[kSDeflateBytes] + 18;
+  ctx->stats.crc32 = (uint32_t)ctx->h_scalars[kSCrc];
+  return DSG_OK;
+}
+
+int dsg_dev_gzip(dsg_ctx *ctx, const uint8_t *d_in, size_t len, int level, uint8_t *d_out, size_t out_cap,
+                 size_t *out_len) {
+  if (!ctx || !out_len || !d_out || (len && !d_in)) return DSG_E_ARG;
+  if (level != DSG_LEVEL_STORED && level != DSG_LEVEL_DEFAULT) return fail(ctx, DSG_E_ARG, "level must be 0 or 6");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  int rc = begin_call(ctx);
+  if (rc) return rc;
+  uint64_t n = 0;
+  rc = gzip_device(ctx, d_in, len, level, d_out, out_cap, &n);
+  *out_len = (size_t)n;
+  if (rc) return rc;
+  ctx->stats.tar_bytes = len;
+  ctx->stats.out_bytes = n;
+  ctx->stats.ms_deflate = elapsed(ctx, kTimDeflate);
+  ctx->stats.ms_crc = elapsed(ctx, kTimCrc);
+  ctx->stats.ms_gather = elapsed(ctx, kTimGather);
+  ctx->stats.kernel_launches = ctx->launches;
+  return DSG_OK;
+}
+
+// ---- the hot path -----------------------------------------------------------------------------------------------
+
+static int pack_resident(dsg_ctx *ctx, const dsg_entry *d_entries, size_t n, const char *d_strtab, size_t strtab_len,
+                         const uint8_t *d_arena, size_t arena_len, bool gzip, uint8_t *d_out, size_t out_cap,
+                         uint64_t *out_len) {
+  uint64_t T = 0, P = 0;
+  int rc = tar_plan(ctx, d_entries, (uint32_t)n, d_strtab, strtab_len, arena_len, ctx->opts.flags, &T, &P);
+  if (rc) return rc;
+  ctx->stats.entries = n;
+  ctx->stats.payload_bytes = P;
+  ctx->stats.tar_bytes = T;
+  if (!gzip) {
+    *out_len = T;
+    if (T > out_cap) return fail(ctx, DSG_E_CAPACITY, "tar stream needs %llu bytes", (unsigned long long)T);
+    tic(ctx, kTimTar);
+    if ((rc = tar_layout(ctx, d_entries, (uint32_t)n, d_strtab, d_arena, 0, d_out, 0, T))) return rc;
+    toc(ctx, kTimTar);
+    return check_status(ctx);
+  }
+  CU(ctx->d_tar.ensure(T + 64));
+  tic(ctx, kTimTar);
+  if ((rc = tar_layout(ctx, d_entries, (uint32_t)n, d_strtab, d_arena, 0, ctx->d_tar.as<uint8_t>(), 0, T))) return rc;
+  toc(ctx, kTimTar);
+  rc = gzip_device(ctx, ctx->d_tar.as<uint8_t>(), T, ctx->opts.level, d_out, out_cap, out_len);
+  if (rc) return rc;
+  DevStatus st;
+  memcpy(&st, &ctx->h_scalars[kSStatus], sizeof st);
+  if (st.code != 0) return fail(ctx, st.code, "entry %u: %s", st.entry, dsg_strerror(st.code));
+  return DSG_OK;
+}
+
+static void finish_stats(dsg_ctx *ctx, uint64_t out_bytes) {
+  ctx->stats.out_bytes = out_bytes;
+  ctx->stats.ms_plan = elapsed(ctx, kTimPlan);
+  ctx->stats.ms_tar = elapsed(ctx, kTimTar);
+  ctx->stats.ms_deflate = elapsed(ctx, kTimDeflate);
+  ctx->stats.ms_crc = elapsed(ctx, kTimCrc);
+  ctx->stats.ms_gather = elapsed(ctx, kTimGather);
+  ctx->stats.ms_total = elapsed(ctx, kTimTotal);
+  ctx->stats.kernel_launches = ctx->launches;
+}
+
+int dsg_pack_device(dsg_ctx *ctx, const dsg_entry *d_entries, size_t n, const char *d_strtab, size_t strtab_len,
+                    const uint8_t *d_arena, size_t arena_len, uint8_t *d_out, size_t out_cap, size_t *out_len) {
+  if (!ctx || !out_len || !d_out || (n && (!d_entries || !d_strtab)) || n > 0xfffffff0ull) return DSG_E_ARG;
+  std::lock_guard<std::mutex> g(ctx->mu);
+  int rc = begin_call(ctx);
+  if (rc) return rc;
+  tic(ctx, kTimTotal);
+  uint64_t produced = 0;
+  rc = pack_resident(ctx, d_entries, n, d_strtab, strtab_len, d_arena, arena_len, true, d_out, out_cap, &produced);
+  *out_len = (size_t)produced;
+  if (rc) return rc;
+  toc(ctx, kTimTotal);
+  CU(cudaStreamSynchronize(ctx->stream));
+  finish_stats(ctx, produced);
+  return DSG_OK;
+}
+
+// Host buffers in, host buffer out.
+static int pack_host_pipelined(dsg_ctx *ctx, const dsg_entry *entries, size_t n, const char *strtab, size_t strtab_len,
+                               const uint8_t *arena, size_t arena_len, bool gzip, uint8_t *out, size_t out_cap,
+                               size_t *out_len) {
+  tic(ctx, kTimTotal);
+  CU(ctx->d_entries.ensure(sizeof(dsg_entry) * std::max<size_t>(n, 1)));
+  CU(ctx->d_strtab.ensure(std::max<size_t>(strtab_len, 1)));
+  CU(ctx->d_arena.ensure(std::max<size_t>(arena_len, 1)));
+  if (n) CU(cudaMemcpyAsync(ctx->d_entries.p, entries, sizeof(dsg_entry) * n, cudaMemcpyHostToDevice, ctx->stream));
+  if (strtab_len) CU(cudaMemcpyAsync(ctx->d_strtab.p, strtab, strtab_len, cudaMemcpyHostToDevice, ctx->stream));
+  if (arena_len) CU(cudaMemcpyAsync(ctx->d_arena.p, arena, arena_len, cudaMemcpyHostToDevice, ctx->stream));
+  ctx->stats.h2d_bytes = sizeof(dsg_entry) * n + strtab_len + arena_len;
+  // size the device output from the plan (host-side helper is O(n); the device plan is authoritative)
+  uint64_t T = 0;
+  int rc = dsg_tar_size(entries, n, strtab, strtab_len, ctx->opts.flags, &T);
+  if (rc) return fail(ctx, rc, "manifest rejected: %s", dsg_strerror(rc));
+  const uint64_t need = gzip ? dsg_gzip_bound(T) : T;
+  CU(ctx->d_out.ensure(need + 64));
+  uint64_t produced = 0;
+  rc = pack_resident(ctx, ctx->d_entries.as<dsg_entry>(), n, ctx->d_strtab.as<char>(), strtab_len,
+                     ctx->d_arena.as<uint8_t>(), arena_len, gzip, ctx->d_out.as<uint8_t>(), need, &produced);
+  *out_len = (size_t)produced;
+  if (rc) return rc;
+  if (produced > out_cap) return fail(ctx, DSG_E_CAPACITY, "output needs %llu bytes", (unsigned long long)produced);
+  CU(cudaMemcpyAsync(out, ctx->d_out.p, produced, cudaMemcpyDeviceToHost, ctx->stream));
+  toc(ctx, kTimTotal);
+  CU(cudaStreamSynchronize(ctx->stream));
+  ctx->stats.d2h_bytes = produced;
+  ctx->stats.segments = 1;
+  finish_stats(ctx, produced);
+  return DSG_OK;
+}
+
+static int pack_host(dsg_ctx *ctx, const dsg_entry *entries, size_t n, const char *strtab, size_t strtab_len,
+                     const uint8_t *arena, size_t arena_len, bool gzip, uint8_t *out, size_t out_cap, size_t *out_len) {
+  if (!ctx || !out_len || !out || (n && (!entries || !strtab)) || (arena_len && !arena) || n > 0xfffffff0ull)
+    return DSG_E_ARG;
+  std::lock_guard<std::mutex> g(ctx->mu);
+  int rc = begin_call(ctx);
+  if (rc) return rc;
+  return pack_host_pipelined(ctx, entries, n, strtab, strtab_len, arena, arena_len, gzip, out, out_cap, out_len);
+}
+
+int dsg_pack(dsg_ctx *ctx, const dsg_entry *entries, size_t n, const char *strtab, size_t strtab_len,
+             const uint8_t *arena, size_t arena_len, uint8_t *out, size_t out_cap, size_t *out_len) {
+  return pack_host(ctx, entries, n, strtab, strtab_len, arena, arena_len, true, out, out_cap, out_len);
+}
+
+int dsg_pack_tar_only(dsg_ctx *ctx, const dsg_entry *entries, size_t n, const char *strtab, size_t strtab_len,
+                      const uint8_t *arena, size_t arena_len, uint8_t *out, size_t out_cap, size_t *out_len) {
+  return pack_host(ctx, entries, n, strtab, strtab_len, arena, arena_len, false, out, out_cap, out_len);
+}
+
+int dsg_get_stats(const dsg_ctx *ctx, dsg_stats *out) {
+  if (!ctx || !out) return DSG_E_ARG;
+  *out = ctx->stats;
+  return DSG_OK;
+}
+
+}  // extern "C"
