@@ -1,0 +1,381 @@
+#!/usr/bin/env python
+"""bench.py -- tar.gz pack throughput (uncompressed payload GB/s) on N B200s, the metric of BASELINE.json.
+
+One step = one pack of the rank's shard of BASELINE config 4 ("synthetic build context with large binaries:
+256 files x 256 MB, file-sharded"): 32 files x 256 MiB per GPU, so N=8 is the full 256-file / 64 GiB config
+and the scaling is weak. Two timed legs per rank, same inputs:
+  value : dsg_pack_device -- manifest + arena already resident in HBM, output left in HBM (CUDA events)
+  e2e   : dsg_pack        -- the call the Go shim makes: pinned host arena in, pinned host .tar.gz out,
+                             H2D and D2H inside the timed region (wall clock around the call)
+plus `roofline` for the dominant kernel (lz_deflate_kernel) and `cpu_baseline` (the CPU oracle, tar + zlib-6,
+on a bounded sample of the same bytes; rank 0, N=1 only).
+`--impl reference` times the reference's CPU path instead (oracle port: Go is absent from the image), file
+sharded over the host threads, on the same workload; rank 0 only.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+import zlib
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+FILE_BYTES = 256 << 20
+FILES_PER_GPU = 32
+METRIC = "tar.gz pack GB/s (uncompressed payload input)"
+UNIT = "GB/s"
+
+
+def env_int(name, default):
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self) -> dict:
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def make_shard(rank: int, files: int, file_bytes: int, device):
+    """Manifest for this rank's files of config 4 + the arena as a torch tensor on `device`."""
+    import torch
+    from devspace_b200 import synth
+    sizes = np.full(files, file_bytes, np.int64)
+    offs, alen = synth._layout(sizes)
+    arena = torch.empty(max(alen, 16), dtype=torch.uint8, device=device)
+    for i in range(files):
+        gi = rank * files + i
+        arena[int(offs[i]): int(offs[i]) + file_bytes] = synth.binary_like(file_bytes, synth.SEED0 + 4 + 31 * gi, device)
+    man = synth.build_manifest(synth.tree_c4_names(files, rank * files), sizes, np.zeros(16, np.uint8), offs)
+    return man, arena
+
+
+def oracle_entries(man, arena_np, lo, hi):
+    import oracle
+    es = []
+    for i in range(lo, hi):
+        e = man.entries[i]
+        o, s = int(e["data_off"]), int(e["size"])
+        es.append(oracle.Entry(name=man.name(i), size=s, mtime_sec=int(e["mtime_sec"]), mtime_nsec=int(e["mtime_nsec"]),
+                               mode=int(e["mode"]), uid=int(e["uid"]), gid=int(e["gid"]), uname=b"dev", gname=b"dev",
+                               data=arena_np[o:o + s]))
+    return es
+
+
+def cpu_pack_seconds(es):
+    """The reference's CPU path for a list of headers: tar stream + gzip (zlib level 6), one thread."""
+    import oracle
+    t0 = time.perf_counter()
+    tar = oracle.tar_stream(es)
+    n = oracle.gzip_pack_size(np.frombuffer(tar, np.uint8))
+    return time.perf_counter() - t0, len(tar), n
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return 0
+    import torch
+    import oracle
+    oracle.build()
+    threads = min(os.cpu_count() or 1, 32)
+    dev = "cuda" if torch.cuda.is_available() else "cpu"
+    files = threads  # one 256 MiB file per host thread and step (file sharded, like the multi-GPU path)
+    file_bytes = env_int("DSG_BENCH_REF_FILE_BYTES", 128 << 20)
+    man, arena = make_shard(0, files, file_bytes, dev)
+    arena_np = arena.cpu().numpy()
+    del arena
+    shards = [oracle_entries(man, arena_np, i, i + 1) for i in range(files)]
+    payload = files * file_bytes
+
+    def step():
+        res = [None] * files
+        ths = [threading.Thread(target=lambda k=k: res.__setitem__(k, cpu_pack_seconds(shards[k]))) for k in range(files)]
+        t0 = time.perf_counter()
+        for t in ths:
+            t.start()
+        for t in ths:
+            t.join()
+        return time.perf_counter() - t0
+
+    for _ in range(max(1, min(args.warmup, 1))):  # the CPU path has no warm-up effects worth minutes of wall time
+        step()
+    times = [step() for _ in range(args.steps)]
+    sec = sum(times) / len(times)
+    v = payload / 1e9 / sec
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "C4 build context: 256 MiB-class ELF-like binaries, file sharded",
+                   "files_per_step": files, "file_bytes": file_bytes, "level": 6},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": f"{files} files x {file_bytes >> 20} MiB per step, one file per host thread; "
+                                   "CPU restatement of archive/tar + gzip (zlib level 6), Go toolchain absent"},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--files", type=int, default=env_int("DSG_BENCH_FILES", FILES_PER_GPU))
+    ap.add_argument("--file-bytes", type=int, default=env_int("DSG_BENCH_FILE_BYTES", FILE_BYTES))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = env_int("RANK", 0)
+    world = env_int("WORLD_SIZE", 1)
+    local = env_int("LOCAL_RANK", 0)
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+
+    import torch
+    import torch.distributed as dist
+    from devspace_b200._lib import DsgError
+    from devspace_b200.pack import DeviceBuffer, Packer
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the pack path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def allmax(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def allsum(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    # shrink the shard if the host cannot pin it (the 8-rank run pins 8 arenas + 8 outputs on one box)
+    files, fbytes = args.files, args.file_bytes
+    try:
+        avail = int([l for l in open("/proc/meminfo") if l.startswith("MemAvailable")][0].split()[1]) * 1024
+        while files > 1 and files * fbytes * 1.7 * world > 0.6 * avail:
+            files //= 2
+    except Exception:
+        pass
+
+    man, arena_dev = make_shard(rank, files, fbytes, dev)
+    P = files * fbytes
+    packer = Packer(device=local, level=6)
+    T = packer.tar_size(man)
+    bound = packer.gzip_bound(T)
+    # --- kernel-only leg buffers (device resident) -----------------------------------------------------------
+    d_entries = DeviceBuffer(packer, man.entries.nbytes).upload(man.entries.view(np.uint8).reshape(-1))
+    d_strtab = DeviceBuffer(packer, man.strtab.size).upload(man.strtab)
+    d_out = DeviceBuffer(packer, int(bound * 0.62) + (1 << 20))
+    lib, ctx = packer._lib, packer._ctx
+
+    def step_resident():
+        n_out = ctypes.c_size_t()
+        rc = lib.dsg_pack_device(ctx, d_entries.ptr, man.n, d_strtab.ptr, man.strtab.size,
+                                 ctypes.c_void_p(arena_dev.data_ptr()), arena_dev.numel(), d_out.ptr, d_out.nbytes,
+                                 ctypes.byref(n_out))
+        packer._check(rc)
+        return n_out.value, packer.stats()
+
+    # --- e2e leg buffers (pinned host) ---------------------------------------------------------------------------
+    h_arena = packer.pinned(arena_dev.numel())
+    torch.from_numpy(h_arena.array).copy_(arena_dev)
+    torch.cuda.synchronize()
+    h_out = packer.pinned(int(bound * 0.62) + (1 << 20))
+    man_host = type(man)(man.entries, man.strtab, h_arena.array)
+
+    def step_e2e():
+        t0 = time.perf_counter()
+        n = packer.pack_into(man_host, h_out.array)
+        dt = time.perf_counter() - t0
+        return n, dt, packer.stats()
+
+    # --- warm-up (also sizes every internal buffer), then the two timed legs ----------------------------------------
+    for _ in range(args.warmup):
+        step_resident()
+    for _ in range(args.warmup):
+        step_e2e()
+    sampler = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    ms_dev, ms_deflate, launches, out_bytes = 0.0, 0.0, 0, 0
+    t_wall0 = time.perf_counter()
+    for _ in range(args.steps):
+        n, st = step_resident()
+        ms_dev += st["ms_total"]
+        ms_deflate += st["ms_deflate"]
+        launches += st["kernel_launches"]
+        out_bytes = n
+    barrier()
+    wall_res = time.perf_counter() - t_wall0
+    barrier()
+    e2e_s, h2d, d2h, launches_e2e, e2e_out = 0.0, 0, 0, 0, 0
+    for _ in range(args.steps):
+        n, dt, st = step_e2e()
+        e2e_s += dt
+        h2d, d2h = st["h2d_bytes"], st["d2h_bytes"]
+        launches_e2e += st["kernel_launches"]
+        e2e_out = n
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+
+    t_res = allmax(ms_dev / 1e3)           # seconds for K steps, slowest rank (CUDA events inside the library)
+    t_wall = allmax(wall_res)
+    t_e2e = allmax(e2e_s)
+    tot_payload = allsum(float(P))
+    value = tot_payload * args.steps / 1e9 / t_res
+    e2e_value = tot_payload * args.steps / 1e9 / t_e2e
+
+    # --- parity spot check on the timed e2e output: first 32 MiB must gunzip to the oracle's tar prefix -------------
+    parity = None
+    size_ratio = None
+    cpu_baseline = None
+    if rank == 0:
+        import oracle
+        oracle.build()
+        arena_np = h_arena.array
+        want = oracle.tar_stream(oracle_entries(man, arena_np, 0, 1))[: 32 << 20]
+        got = zlib.decompressobj(31).decompress(h_out.array[: min(e2e_out, 64 << 20)].tobytes(), len(want))
+        parity = bool(got == want)
+        if world == 1 and not args.no_cpu_baseline:
+            k = max(1, min(files, (512 << 20) // fbytes))
+            sec, tlen, clen = cpu_pack_seconds(oracle_entries(man, arena_np, 0, k))
+            cpu_baseline = {"value": k * fbytes / 1e9 / sec, "unit": UNIT, "cores": 1, "kind": "port",
+                            "sample": f"first {k} of {files} files ({k * fbytes >> 20} MiB) of the same arena; CPU "
+                                      "restatement of archive/tar + compress/gzip (zlib level 6), single thread like "
+                                      "the reference's single goroutine; Go toolchain absent from the image"}
+            # compressed size against the oracle on that sample (judged: <= 1.03)
+            sub = type(man)(man.entries[:k], man.strtab, arena_np)
+            n_sub = packer.pack_into(sub, h_out.array)
+            size_ratio = n_sub / clen
+    hbm_peak, peak_src = measured_peaks()
+    C = out_bytes - 18
+    alg_bytes = T + C                       # deflate kernel: reads the tar stream once, writes the compressed bytes
+    defl_ms = ms_deflate / args.steps
+    achieved = alg_bytes / 1e6 / defl_ms if defl_ms > 0 else 0.0
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": t_res * 1e3 / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8", "data": "synthetic",
+        "config": {"workload": f"C4 build context shard: {files} files x {fbytes >> 20} MiB ELF-like binaries per GPU "
+                               f"(N=8 x 32 files = the 256-file / 64 GiB config)", "files_per_gpu": files,
+                   "file_bytes": fbytes, "level": 6, "payload_bytes_per_gpu": P, "tar_bytes_per_gpu": T,
+                   "gzip_bytes_per_gpu": out_bytes, "l2": "inputs (>= 8 GiB per step) far exceed the 126 MB L2",
+                   "timing": "value: CUDA events in libdsgpack (dsg_stats.ms_total), max over ranks; e2e: wall clock "
+                             "around dsg_pack, max over ranks"},
+        "wall_ms_per_step_resident": t_wall * 1e3 / args.steps,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": t_e2e * 1e3 / args.steps,
+                "pcie_h2d_roofline_frac": (h2d / 1e9 / (t_e2e / args.steps)) / 55.6,
+                "pcie_h2d_peak_GBps": 55.6, "pcie_peak_source": "profiles/r01_microbench.jsonl (pinned cudaMemcpyAsync, 1 GiB)"},
+        "gpu_launches": launches + launches_e2e,
+        "roofline": {"kernel": "lz_deflate_kernel", "bound": "hbm", "achieved": achieved, "peak": hbm_peak,
+                     "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": alg_bytes,
+                     "note": "the kernel is bound by shared-memory bandwidth / LSU issue (random 1-2 byte probes of "
+                             "the hash chains), not by HBM; see profiles/ for the ncu stall breakdown"},
+        "cpu_baseline": cpu_baseline,
+        "clocks": clocks,
+        "parity_spot_check": parity,
+        "size_ratio_vs_zlib6": size_ratio,
+    }
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    for b in (d_entries, d_strtab, d_out):
+        b.free()
+    h_arena.free()
+    h_out.free()
+    packer.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

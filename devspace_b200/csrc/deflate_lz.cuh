@@ -1,13 +1,726 @@
-// deflate_lz.cuh -- LZ77 + dynamic Huffman deflate kernels (compress/flate level 6 equivalent).
+// deflate_lz.cuh -- block-parallel DEFLATE for sm_100a: LZ77 match finding in shared memory, per-chunk dynamic
+// Huffman tables, warp-scan bit packing; the compress/flate level-6 writer behind gzip.NewWriter
+// (/root/reference/pkg/devspace/sync/tar.go:156) re-designed for the GPU [Go stdlib compress/flate is not
+// vendored; the published algorithm family and level-6 parameters are restated in oracle/gogzip.c].
+//
+// Stream structure (pigz style, BASELINE.json north_star): the input is cut into 64 KiB chunks. A chunk is
+// compressed by one CTA into one deflate block (dynamic, fixed or stored, whichever is smallest) followed by an
+// empty stored block (sync flush marker 00 00 ff ff) so that every chunk ends on a byte boundary and chunks
+// concatenate by byte copy. The previous 32 KiB of INPUT serve as the chunk's dictionary (same member, so
+// back-references into it are legal), which keeps the size within ~1 % of a serial level-6 stream.
+//
+// One persistent kernel (grid = #SMs, 512 threads, ~200 KB shared memory, 1 CTA/SM):
+//   per chunk   ticket = atomicAdd(counter)                        (chunks start in index order)
+//   per 8 KiB tile of the chunk:
+//     load      tile bytes -> shared-memory ring (dictionary 32 KiB + tile 8 KiB + look-ahead)
+//     insert    hash of 4 bytes -> head[8192] via atomicExch, prev[] links as 16-bit ring slots
+//               (shared-memory atomicExch measured at LDS rate on B200: profiles/r01_microbench.jsonl)
+//     search    one thread per run of 16 consecutive positions walks the hash chain (depth <= 48, nice 128,
+//               good 8); a position inherits (len-1, dist) from its predecessor, so positions inside a long
+//               match cost one probe instead of a full compare
+//     parse     stateless lazy rule next(p) = p + (len[p] >= 4 && len[p+1] <= len[p] ? len[p] : 1); the orbit of
+//               the chunk start under next() is found by 32 lanes parsing 256-position sub-ranges
+//               speculatively and a serial fix-up that stops at the first already-marked position
+//     emit      token starts -> block-wide rank (scan) -> 32-bit tokens to a per-CTA global scratch (L2
+//               resident) + shared-memory histograms
+//   per chunk   Huffman code lengths (two-queue merge, zlib-style overflow repair), code-length RLE, exact
+//               sizes of the three encodings -> chunk size known BEFORE any bit is written
+//               decoupled look-back over the previous chunks' sizes -> output offset (no gather pass)
+//               bit packing: per-token bit lengths -> block scan -> atomicOr into a shared-memory window ->
+//               realigned 128-bit stores to the final position
+// Roofline: the kernel is bound by shared-memory bandwidth / LSU issue (random 1-2 byte reads), not by HBM:
+// algorithmic HBM bytes per chunk are 64 KiB read (+32 KiB dictionary re-read from L2) + C written.
 #pragma once
 
-#include "dsg_common.cuh"
+#include "copy_util.cuh"
 #include "deflate_stored.cuh"
+#include "huffman.cuh"
 
 namespace dsg {
 
-// Upper bound of the raw deflate output for n input bytes (any level): a chunk never exceeds its
-// stored encoding, plus the 2-byte terminator.
-DSG_HD uint64_t lz_deflate_bound(uint64_t n) { return stored_deflate_size(n) + 64; }
+constexpr int kLzThreads = 512;
+constexpr int kLzWarps = kLzThreads / 32;
+constexpr int kChunk = 65536;
+constexpr int kTile = 8192;
+constexpr int kDict = 32768;
+constexpr int kRing = kDict + kTile;     // 40960 ring slots (bytes)
+constexpr int kLook = 272;               // look-ahead beyond a tile (>= 258 + 3, multiple of 16)
+constexpr int kMaxDist = kDict - kLook;  // 32496
+constexpr int kHashBits = 13;
+constexpr int kHashSize = 1 << kHashBits;
+constexpr int kMinMatch = 4;
+constexpr int kMaxMatch = 258;
+constexpr int kDepth = 48;
+constexpr int kNice = 128;
+constexpr int kGood = 8;
+constexpr int kRun = kTile / kLzThreads;  // 16 consecutive positions per thread
+constexpr int kSub = kTile / 32;          // 256 positions per parse lane
+constexpr uint16_t kNil = 0xffff;
+constexpr int kStageBytes = 16384;        // bit-packing window
+constexpr int kBatchTokens = 2048;        // tokens per bit-packing batch (<= 48 bits each = 12 KiB)
+constexpr int kTokPerThread = kBatchTokens / kLzThreads;
+constexpr uint32_t kTokMatch = 0x80000000u;
+constexpr int kTokSlotWords = kChunk + 64;  // per-CTA token scratch (u32), worst case all literals + EOB
+
+// Upper bound of the raw deflate output for n input bytes: a chunk never exceeds its stored encoding
+// (two stored blocks for a 64 KiB chunk), plus the 2-byte terminator.
+DSG_HD uint64_t lz_deflate_bound(uint64_t n) { return n + 10 * ((n + kChunk - 1) / kChunk) + 2 + 64; }
+
+// Shared-memory carve-up (dynamic shared memory; byte offsets, 16-byte aligned)
+struct LzLayout {
+  static constexpr int data = 0;                                  // kRing + kLook + 48 bytes (mirror + slack)
+  static constexpr int prev = data + kRing + kLook + 48;          // u16[kRing]
+  static constexpr int head = prev + 2 * kRing;                   // u32[kHashSize]; Huffman scratch afterwards
+  static constexpr int mlen = head + 4 * kHashSize;               // u8[kTile]      } reused as the bit-packing
+  static constexpr int mdist = mlen + kTile;                      // u16[kTile]     } window after the last tile
+  static constexpr int bitmap = mdist + 2 * kTile;                // u32[kTile/32] token-start flags
+  static constexpr int lfreq = bitmap + kTile / 8;                // u32[288]
+  static constexpr int dfreq = lfreq + 4 * 288;                   // u32[32]
+  static constexpr int llen = dfreq + 4 * 32;                     // u8[288] literal/length code lengths
+  static constexpr int dlen = llen + 288;                         // u8[32]
+  static constexpr int lcode = dlen + 32;                         // u16[288]
+  static constexpr int dcode = lcode + 2 * 288;                   // u16[32]
+  static constexpr int cllen = dcode + 2 * 32;                    // u8[32]
+  static constexpr int clcode = cllen + 32;                       // u16[32]
+  static constexpr int rle = clcode + 2 * 32;                     // u16[320]
+  static constexpr int misc = rle + 2 * 320;                      // u32[64] scalars / scan scratch
+  static constexpr int total = misc + 4 * 64 + 16;
+};
+static_assert(LzLayout::prev % 16 == 0 && LzLayout::head % 16 == 0 && LzLayout::mlen % 16 == 0, "alignment");
+static_assert(kTile + 2 * kTile >= kStageBytes, "bit-packing window must fit in the match arrays");
+static_assert(sizeof(HuffScratch) * 2 + 512 <= 4 * kHashSize, "Huffman scratch must fit in the head table");
+static_assert(LzLayout::total <= 227 * 1024, "shared memory budget");
+static_assert(kMaxDist % 16 == 0 && kLook % 16 == 0, "ring loads move 16-byte granules");
+
+// misc[] slots
+enum { kMTicket = 0, kMStart, kMNTok, kMMode, kMOutLo, kMOutHi, kMHdrBits, kMChunkBytes, kMHlit, kMHdist, kMHclen,
+       kMNRle, kMBodyDyn, kMBodyFix, kMError, kMScan = 32 /* 16 warp partials + carry */ };
+
+// Kernel parameter block
+struct LzParams {
+  const uint8_t *in;          // input stream (this call's bytes)
+  uint64_t len;               // bytes
+  const uint8_t *dict;        // up to 32 KiB that precede `in` in the member (previous segment), or null
+  uint32_t dict_len;
+  uint8_t *out;               // output base
+  uint64_t out_cap;
+  uint32_t nchunks;
+  uint32_t *ticket;           // zeroed before launch
+  unsigned long long *state;  // per chunk look-back word: (bytes << 2) | flag; zeroed before launch
+  uint32_t *tok_scratch;      // gridDim.x * kTokSlotWords
+  uint64_t *total_out;        // deflate bytes produced by this launch (written by the last chunk's CTA)
+  uint32_t *error;            // set to 1 when out_cap is too small
+  int write_terminator;       // append the final empty fixed block (03 00)
+};
+
+DSG_D uint32_t ring_slot(int rp /* chunk-relative position, >= -kDict */) {
+  uint32_t x = (uint32_t)(rp + kDict);
+  if (x >= 2u * kRing) x -= 2u * kRing;
+  else if (x >= (uint32_t)kRing) x -= kRing;
+  return x;
+}
+
+DSG_D uint32_t hash4(uint32_t v) { return (v * 2654435761u) >> (32 - kHashBits); }
+
+// 4 bytes at an arbitrary shared-memory byte offset (little endian)
+DSG_D uint32_t load4(const uint8_t *p) {
+  const uint32_t m = (uint32_t)((uintptr_t)p & 3);
+  const uint32_t *a = reinterpret_cast<const uint32_t *>(p - m);
+  uint32_t lo = a[0];
+  if (m == 0) return lo;
+  uint32_t hi = a[1];
+  return __funnelshift_r(lo, hi, 8 * m);
+}
+
+// Block-wide exclusive scan of one value per thread (512 threads). Returns the exclusive prefix and the
+// block total through *total. `scratch` has >= 17 words. Two barriers.
+DSG_D uint32_t block_exclusive_scan(uint32_t v, uint32_t *scratch, uint32_t *total) {
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t x = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= (uint32_t)o) x += y;
+  }
+  if (lane == 31) scratch[warp] = x;
+  __syncthreads();
+  if (warp == 0) {
+    uint32_t t = lane < (uint32_t)kLzWarps ? scratch[lane] : 0;
+    uint32_t s = t;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t y = __shfl_up_sync(0xffffffffu, s, o);
+      if (lane >= (uint32_t)o) s += y;
+    }
+    if (lane < (uint32_t)kLzWarps) scratch[lane] = s - t;
+    if (lane == kLzWarps - 1) scratch[kLzWarps] = s;
+  }
+  __syncthreads();
+  uint32_t r = scratch[warp] + (x - v);
+  *total = scratch[kLzWarps];
+  return r;
+}
+
+// Sequential LSB-first bit writer into a zeroed shared-memory window (single thread).
+struct SmemBitWriter {
+  uint32_t *w;
+  uint32_t pos;  // bit position
+  DSG_D void put(uint32_t v, uint32_t n) {
+    if (n == 0) return;
+    uint32_t i = pos >> 5, s = pos & 31;
+    w[i] |= v << s;
+    if (s + n > 32) w[i + 1] |= v >> (32 - s);
+    pos += n;
+  }
+};
+
+// ---------------------------------------------------------------------------------------------------------
+// tile phases
+// ---------------------------------------------------------------------------------------------------------
+
+// Copies stream bytes [g0, g1) (absolute offsets in the call's input, may be negative = dictionary from the
+// previous segment, may exceed len = zero fill) to the ring slots of chunk-relative positions rp0...
+DSG_D void load_ring(uint8_t *s_data, const LzParams &P, int64_t cs, int rp0, int rp1) {
+  // 16-byte granules: rp0 and rp1 are multiples of 16 and the ring size is a multiple of 16
+  for (int rp = rp0 + 16 * (int)threadIdx.x; rp < rp1; rp += 16 * kLzThreads) {
+    const int64_t g = cs + rp;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (g >= 0 && g + 16 <= (int64_t)P.len && (((uintptr_t)(P.in + g)) & 15) == 0) {
+      v = *reinterpret_cast<const uint4 *>(P.in + g);
+    } else {
+      uint32_t w[4] = {0, 0, 0, 0};
+      for (int k = 0; k < 16; k++) {
+        const int64_t gg = g + k;
+        uint32_t b = 0;
+        if (gg >= 0) {
+          if (gg < (int64_t)P.len) b = P.in[gg];
+        } else if (P.dict && -gg <= (int64_t)P.dict_len) {
+          b = P.dict[(int64_t)P.dict_len + gg];
+        }
+        w[k >> 2] |= b << (8 * (k & 3));
+      }
+      v = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+    const uint32_t slot = ring_slot(rp);
+    *reinterpret_cast<uint4 *>(s_data + slot) = v;
+    if (slot < (uint32_t)(kLook + 48)) {  // mirror of the ring start behind its end: reads never wrap
+      if (slot + 16 <= (uint32_t)(kLook + 48)) *reinterpret_cast<uint4 *>(s_data + kRing + slot) = v;
+    }
+  }
+}
+
+// Inserts positions [rp0, rp1) into the hash chains, 512 consecutive positions per round.
+DSG_D void insert_positions(const uint8_t *s_data, uint16_t *s_prev, uint32_t *s_head, int rp0, int rp1) {
+  for (int base = rp0; base < rp1; base += kLzThreads) {
+    const int rp = base + (int)threadIdx.x;
+    if (rp < rp1) {
+      const uint32_t slot = ring_slot(rp);
+      const uint32_t h = hash4(load4(s_data + slot));
+      const uint32_t old = atomicExch(&s_head[h], slot);
+      s_prev[slot] = (uint16_t)old;
+    }
+    __syncthreads();  // rounds are ordered; inside a round the order of equal hashes is arbitrary
+  }
+}
+
+// Longest match for every position of the tile. tile_rp = chunk-relative position of the tile start,
+// chunk_len = bytes in this chunk, lo_rp = lowest chunk-relative position holding real data (-dictionary).
+DSG_D void search_tile(const uint8_t *s_data, const uint16_t *s_prev, uint8_t *s_mlen, uint16_t *s_mdist, int tile_rp,
+                       int chunk_len, int lo_rp) {
+  const int t0 = (int)threadIdx.x * kRun;
+  int inh_len = 0, inh_dist = 0;
+#pragma unroll 1
+  for (int j = 0; j < kRun; j++) {
+    const int tp = t0 + j;      // tile-relative
+    const int rp = tile_rp + tp;  // chunk-relative
+    int best = 0, bdist = 0;
+    const int maxlen = chunk_len - rp < kMaxMatch ? chunk_len - rp : kMaxMatch;
+    if (maxlen >= kMinMatch) {
+      if (inh_len > kMinMatch) {
+        best = inh_len - 1;
+        bdist = inh_dist;
+        if (best > maxlen) best = maxlen;
+      }
+      int depth = kDepth;
+      if (best >= kNice) depth = 0;
+      else if (best >= kGood) depth = kDepth / 4;
+      const uint32_t slot = ring_slot(rp);
+      const uint8_t *a = s_data + slot;
+      const int max_back = rp - lo_rp < kMaxDist ? rp - lo_rp : kMaxDist;  // farthest usable distance
+      uint32_t q = s_prev[slot];
+      uint8_t a_hi = a[best], a_lo = best ? a[best - 1] : 0;
+      while (depth-- > 0 && q != kNil) {
+        int d = (int)slot - (int)q;
+        if (d <= 0) d += kRing;
+        if (d > max_back) {
+          if (d > kRing - 2 * kLzThreads) {  // inserted in the same round but later in the stream: skip
+            q = s_prev[q];
+            continue;
+          }
+          break;  // outside the window (or a stale link)
+        }
+        const uint8_t *b = s_data + q;
+        if (b[best] == a_hi && (best == 0 || b[best - 1] == a_lo)) {
+          int l = 0;
+          while (l < maxlen && a[l] == b[l]) l++;
+          if (l >= kMinMatch && (l > best || (l == best && d < bdist))) {
+            best = l;
+            bdist = d;
+            if (l >= kNice || l >= maxlen) break;
+            a_hi = a[best];
+            a_lo = a[best - 1];
+          }
+        }
+        q = s_prev[q];
+      }
+      if (best < kMinMatch) best = 0;
+    }
+    s_mlen[tp] = (uint8_t)(best ? best - 3 : 0);  // 0 = no match, else len-3 in 1..255
+    s_mdist[tp] = (uint16_t)bdist;
+    inh_len = best;
+    inh_dist = bdist;
+  }
+}
+
+// next(p) for the stateless lazy parse; tp is tile-relative, tile_len = positions of this tile inside the chunk
+DSG_D int parse_step(const uint8_t *s_mlen, int tp, int tile_len) {
+  const uint32_t l = s_mlen[tp];
+  if (l == 0) return 1;
+  if (tp + 1 < tile_len && s_mlen[tp + 1] > l) return 1;  // a longer match starts at the next byte: defer
+  return (int)l + 3;
+}
+
+DSG_D void clear_bits(uint32_t *bm, int lo, int hi) {  // clears bits [lo, hi)
+  for (int p = lo; p < hi;) {
+    const int w = p >> 5, b = p & 31;
+    const int n = (32 - b) < (hi - p) ? (32 - b) : (hi - p);
+    const uint32_t mask = (n == 32 ? 0xffffffffu : ((1u << n) - 1u)) << b;
+    bm[w] &= ~mask;
+    p += n;
+  }
+}
+
+// Marks the token start positions of the tile in s_bitmap. `start` = first token start (tile-relative, may
+// lie beyond the tile). Returns the first token start of the following tile (relative to that tile).
+// Executed by warp 0 only.
+DSG_D int parse_tile_warp0(const uint8_t *s_mlen, uint32_t *s_bitmap, int start, int tile_len) {
+  const int lane = (int)(threadIdx.x & 31);
+  const int sub_lo = lane * kSub;
+  const int sub_hi = (sub_lo + kSub < tile_len) ? sub_lo + kSub : tile_len;
+  uint32_t *bm = s_bitmap;  // each lane owns words [lane*8, lane*8+8)
+  for (int w = 0; w < kSub / 32; w++) bm[lane * (kSub / 32) + w] = 0;
+  // speculative walk from the sub-range start (lane 0: from the true start)
+  int p = lane == 0 ? start : sub_lo;
+  while (p < sub_hi) {
+    bm[p >> 5] |= 1u << (p & 31);
+    p += parse_step(s_mlen, p, tile_len);
+  }
+  const int exit_p = p;  // first token start at or beyond the end of the sub-range
+  __syncwarp();
+  // serial fix-up: lane l learns where lane l-1 really ended
+  int true_in = exit_p;  // lane 0's exit is final
+  for (int l = 1; l < 32; l++) {
+    const int prev_exit = __shfl_sync(0xffffffffu, true_in, l - 1);
+    if (lane == l) {
+      if (sub_lo >= tile_len) {
+        true_in = prev_exit;  // nothing here; pass through
+      } else if (prev_exit >= sub_hi) {
+        clear_bits(bm, sub_lo, sub_hi);  // the whole sub-range lies inside an earlier match
+        true_in = prev_exit;
+      } else if (prev_exit == sub_lo) {
+        true_in = exit_p;  // speculation was right
+      } else {
+        clear_bits(bm, sub_lo, prev_exit);
+        int q = prev_exit;
+        int out = exit_p;
+        bool converged = false;
+        while (q < sub_hi) {
+          if (bm[q >> 5] & (1u << (q & 31))) {
+            converged = true;
+            break;
+          }
+          bm[q >> 5] |= 1u << (q & 31);
+          const int nq = q + parse_step(s_mlen, q, tile_len);
+          clear_bits(bm, q + 1, nq < sub_hi ? nq : sub_hi);
+          q = nq;
+        }
+        if (!converged) out = q;
+        true_in = out;
+      }
+    }
+    __syncwarp();
+  }
+  const int last_exit = __shfl_sync(0xffffffffu, true_in, 31);
+  return last_exit - tile_len;  // >= 0
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// the kernel
+// ---------------------------------------------------------------------------------------------------------
+
+__global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
+  DSG_DYN_SMEM(smem);
+  uint8_t *s_data = smem + LzLayout::data;
+  uint16_t *s_prev = reinterpret_cast<uint16_t *>(smem + LzLayout::prev);
+  uint32_t *s_head = reinterpret_cast<uint32_t *>(smem + LzLayout::head);
+  uint8_t *s_mlen = smem + LzLayout::mlen;
+  uint16_t *s_mdist = reinterpret_cast<uint16_t *>(smem + LzLayout::mdist);
+  uint32_t *s_bitmap = reinterpret_cast<uint32_t *>(smem + LzLayout::bitmap);
+  uint32_t *s_lfreq = reinterpret_cast<uint32_t *>(smem + LzLayout::lfreq);
+  uint32_t *s_dfreq = reinterpret_cast<uint32_t *>(smem + LzLayout::dfreq);
+  uint8_t *s_llen = smem + LzLayout::llen;
+  uint8_t *s_dlen = smem + LzLayout::dlen;
+  uint16_t *s_lcode = reinterpret_cast<uint16_t *>(smem + LzLayout::lcode);
+  uint16_t *s_dcode = reinterpret_cast<uint16_t *>(smem + LzLayout::dcode);
+  uint8_t *s_cllen = smem + LzLayout::cllen;
+  uint16_t *s_clcode = reinterpret_cast<uint16_t *>(smem + LzLayout::clcode);
+  uint16_t *s_rle = reinterpret_cast<uint16_t *>(smem + LzLayout::rle);
+  uint32_t *s_misc = reinterpret_cast<uint32_t *>(smem + LzLayout::misc);
+  uint32_t *s_stage = reinterpret_cast<uint32_t *>(smem + LzLayout::mlen);  // bit-packing window (after the tiles)
+  uint32_t *tokens = P.tok_scratch + (size_t)blockIdx.x * kTokSlotWords;
+  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+  for (;;) {
+    __syncthreads();  // previous chunk fully done with shared memory
+    if (tid == 0) s_misc[kMTicket] = atomicAdd(P.ticket, 1u);
+    __syncthreads();
+    const uint32_t c = s_misc[kMTicket];
+    if (c >= P.nchunks) break;
+    const int64_t cs = (int64_t)c * kChunk;
+    const int chunk_len = (int)((int64_t)P.len - cs < kChunk ? (int64_t)P.len - cs : kChunk);
+    // dictionary actually available before this chunk; positions farther back than kMaxDist are never
+    // referenced (their ring slots are reused by the first tile's look-ahead)
+    const int64_t avail = cs + (P.dict ? (int64_t)P.dict_len : 0);
+    const int lo_rp = -(int)(avail < (int64_t)kMaxDist ? avail : (int64_t)kMaxDist);
+
+    for (uint32_t i = tid; i < 288; i += kLzThreads) s_lfreq[i] = 0;
+    if (tid < 32) s_dfreq[tid] = 0;
+    for (uint32_t i = tid; i < (uint32_t)kHashSize; i += kLzThreads) s_head[i] = kNil;
+    if (tid == 0) {
+      s_misc[kMStart] = 0;
+      s_misc[kMNTok] = 0;
+    }
+    // dictionary + first tile + look-ahead are resident before the dictionary is hashed (the last three
+    // dictionary positions hash over the first bytes of the chunk). kMaxDist is a multiple of 16.
+    load_ring(s_data, P, cs, -(((-lo_rp) + 15) & ~15), kTile + kLook);
+    __syncthreads();
+    insert_positions(s_data, s_prev, s_head, lo_rp, 0);  // ends with a barrier (or is a no-op)
+    __syncthreads();
+
+    const int ntiles = (chunk_len + kTile - 1) / kTile;
+    for (int t = 0; t < ntiles; t++) {
+      const int tile_rp = t * kTile;
+      const int tile_len = chunk_len - tile_rp < kTile ? chunk_len - tile_rp : kTile;
+      if (t > 0) {  // next tile's bytes + look-ahead replace the oldest dictionary bytes
+        load_ring(s_data, P, cs, tile_rp + kLook, tile_rp + kTile + kLook);
+        __syncthreads();
+      }
+      insert_positions(s_data, s_prev, s_head, tile_rp, tile_rp + tile_len);
+      search_tile(s_data, s_prev, s_mlen, s_mdist, tile_rp, chunk_len, lo_rp);
+      __syncthreads();
+      if (warp == 0) {
+        const int nxt = parse_tile_warp0(s_mlen, s_bitmap, (int)s_misc[kMStart], tile_len);
+        if (lane == 0) s_misc[kMStart] = (uint32_t)nxt;
+      }
+      __syncthreads();
+      // emit tokens: rank of every start position, then token words + histograms
+      {
+        const int t0 = (int)tid * kRun;
+        const uint32_t bits = (s_bitmap[t0 >> 5] >> (t0 & 31)) & 0xffffu;
+        uint32_t total;
+        uint32_t rank = block_exclusive_scan((uint32_t)__popc(bits), s_misc + kMScan, &total);
+        const uint32_t base = s_misc[kMNTok];
+        uint32_t m = bits;
+        while (m) {
+          const int j = __ffs((int)m) - 1;
+          m &= m - 1;
+          const int tp = t0 + j;
+          const uint32_t l = s_mlen[tp];
+          uint32_t tok;
+          // the lazy rule may have deferred a match: a start with a longer match right behind it is a literal
+          const bool lit = l == 0 || (tp + 1 < tile_len && s_mlen[tp + 1] > l);
+          if (lit) {
+            tok = s_data[ring_slot(tile_rp + tp)];
+            atomicAdd(&s_lfreq[tok], 1u);
+          } else {
+            const uint32_t d = s_mdist[tp];
+            tok = kTokMatch | (l << 16) | (d - 1);  // l = len-3
+            atomicAdd(&s_lfreq[257 + len_code(l + 3)], 1u);
+            atomicAdd(&s_dfreq[dist_code(d)], 1u);
+          }
+          tokens[base + rank++] = tok;
+        }
+        __syncthreads();
+        if (tid == 0) s_misc[kMNTok] = base + total;
+        __syncthreads();
+      }
+    }
+
+    // ---- Huffman tables and exact sizes ------------------------------------------------------------------
+    if (tid == 0) {
+      tokens[s_misc[kMNTok]] = kEob;  // end-of-block travels as the last "literal" symbol
+      s_misc[kMNTok] += 1;
+      s_lfreq[kEob] += 1;
+    }
+    __syncthreads();
+    HuffScratch *hs = reinterpret_cast<HuffScratch *>(s_head);
+    if (tid == 0) {
+      int max_l = huff_build_lengths(s_lfreq, kNumLitLen, kMaxBits, s_llen, hs[0]);
+      s_misc[kMHlit] = (uint32_t)((max_l < 256 ? 256 : max_l) + 1);
+      huff_make_codes(s_llen, kNumLitLen, s_lcode);
+    } else if (tid == 32) {
+      int max_d = huff_build_lengths(s_dfreq, kNumDist, kMaxBits, s_dlen, hs[1]);
+      s_misc[kMHdist] = (uint32_t)(max_d + 1);
+      huff_make_codes(s_dlen, kNumDist, s_dcode);
+    }
+    __syncthreads();
+    // body sizes: sum freq * len (+ extra bits) for the dynamic and the fixed code
+    {
+      uint32_t dyn = 0, fix = 0;
+      for (uint32_t s = tid; s < (uint32_t)(kNumLitLen + kNumDist); s += kLzThreads) {
+        if (s < (uint32_t)kNumLitLen) {
+          const uint32_t f = s_lfreq[s];
+          const uint32_t eb = s > 256 ? len_extra_bits(s - 257) : 0;
+          dyn += f * (s_llen[s] + eb);
+          fix += f * (fixed_litlen_bits(s) + eb);
+        } else {
+          const uint32_t dsy = s - kNumLitLen;
+          const uint32_t f = s_dfreq[dsy];
+          const uint32_t eb = dist_extra_bits(dsy);
+          dyn += f * (s_dlen[dsy] + eb);
+          fix += f * (5 + eb);
+        }
+      }
+      for (int o = 16; o > 0; o >>= 1) {
+        dyn += __shfl_xor_sync(0xffffffffu, dyn, o);
+        fix += __shfl_xor_sync(0xffffffffu, fix, o);
+      }
+      if (lane == 0) {
+        s_misc[kMScan + warp] = dyn;
+        s_misc[kMScan + 16 + warp] = fix;
+      }
+    }
+    __syncthreads();
+    if (tid == 0) {
+      uint32_t body_dyn = 0, body_fix = 0;
+      for (int w = 0; w < kLzWarps; w++) {
+        body_dyn += s_misc[kMScan + w];
+        body_fix += s_misc[kMScan + 16 + w];
+      }
+      // code-length code
+      const uint32_t hlit = s_misc[kMHlit], hdist = s_misc[kMHdist];
+      uint8_t *comb = reinterpret_cast<uint8_t *>(hs + 2);  // 316 bytes behind the two tree scratches
+      for (uint32_t i = 0; i < hlit; i++) comb[i] = s_llen[i];
+      for (uint32_t i = 0; i < hdist; i++) comb[hlit + i] = s_dlen[i];
+      uint32_t cf[kNumCodeLen];
+      for (int i = 0; i < kNumCodeLen; i++) cf[i] = 0;
+      const int nr = rle_code_lengths(comb, (int)(hlit + hdist), s_rle, cf);
+      huff_build_lengths(cf, kNumCodeLen, kMaxClBits, s_cllen, hs[0]);
+      huff_make_codes(s_cllen, kNumCodeLen, s_clcode);
+      int hclen = kNumCodeLen;
+      while (hclen > 4 && s_cllen[cl_order(hclen - 1)] == 0) hclen--;
+      uint32_t hdr = 3 + 5 + 5 + 4 + 3 * (uint32_t)hclen;
+      for (int i = 0; i < nr; i++) hdr += s_cllen[s_rle[i] & 0xff] + cl_extra_bits(s_rle[i] & 0xff);
+      const uint32_t dyn_bits = hdr + body_dyn;
+      const uint32_t fix_bits = 3 + body_fix;
+      const uint32_t n_stored_blocks = ((uint32_t)chunk_len + kStoredMax - 1) / kStoredMax;
+      const uint32_t stored_bytes = (uint32_t)chunk_len + 5 * n_stored_blocks;
+      // compressed encodings end with the sync marker: 3 header bits, pad to a byte, 00 00 ff ff
+      const uint32_t dyn_bytes = (dyn_bits + 3 + 7) / 8 + 4;
+      const uint32_t fix_bytes = (fix_bits + 3 + 7) / 8 + 4;
+      uint32_t mode, bytes, hbits;
+      if (stored_bytes <= dyn_bytes && stored_bytes <= fix_bytes) {
+        mode = 0; bytes = stored_bytes; hbits = 0;
+      } else if (fix_bytes <= dyn_bytes) {
+        mode = 1; bytes = fix_bytes; hbits = 3;
+      } else {
+        mode = 2; bytes = dyn_bytes; hbits = hdr;
+      }
+      s_misc[kMMode] = mode;
+      s_misc[kMChunkBytes] = bytes;
+      s_misc[kMHdrBits] = hbits;
+      s_misc[kMHclen] = (uint32_t)hclen;
+      s_misc[kMNRle] = (uint32_t)nr;
+      // decoupled look-back: exclusive prefix of the previous chunks' sizes
+      unsigned long long excl = 0;
+      if (c > 0) {
+        atomicExch(&P.state[c], ((unsigned long long)bytes << 2) | 1ull);
+        int64_t i = (int64_t)c - 1;
+        for (;;) {
+          unsigned long long v;
+          do {
+            v = atomicAdd(&P.state[i], 0ull);
+          } while ((v & 3ull) == 0ull);
+          excl += v >> 2;
+          if ((v & 3ull) == 2ull) break;
+          i--;
+        }
+      }
+      __threadfence();
+      atomicExch(&P.state[c], ((excl + bytes) << 2) | 2ull);
+      s_misc[kMOutLo] = (uint32_t)excl;
+      s_misc[kMOutHi] = (uint32_t)(excl >> 32);
+      uint32_t err = 0;
+      const uint64_t need = excl + bytes + ((c == P.nchunks - 1 && P.write_terminator) ? 2 : 0);
+      if (need > P.out_cap) {
+        err = 1;
+        atomicExch(P.error, 1u);
+      }
+      s_misc[kMError] = err;
+      if (c == P.nchunks - 1) *P.total_out = need;
+    }
+    __syncthreads();
+    const uint32_t mode = s_misc[kMMode];
+    const uint32_t chunk_bytes = s_misc[kMChunkBytes];
+    const uint64_t out_off = (uint64_t)s_misc[kMOutLo] | ((uint64_t)s_misc[kMOutHi] << 32);
+    if (s_misc[kMError]) continue;
+    uint8_t *dst = P.out + out_off;
+
+    if (mode == 0) {
+      // stored: one or two blocks, bytes straight from the input
+      const uint8_t *src = P.in + cs;
+      uint32_t done = 0, o = 0;
+      while (done < (uint32_t)chunk_len) {
+        const uint32_t n = (uint32_t)chunk_len - done < kStoredMax ? (uint32_t)chunk_len - done : kStoredMax;
+        if (tid == 0) {
+          dst[o + 0] = 0;
+          dst[o + 1] = (uint8_t)(n & 0xff);
+          dst[o + 2] = (uint8_t)(n >> 8);
+          dst[o + 3] = (uint8_t)(~n & 0xff);
+          dst[o + 4] = (uint8_t)((~n >> 8) & 0xff);
+        }
+        block_copy_unaligned(dst + o + 5, src + done, n, tid, kLzThreads);
+        done += n;
+        o += n + 5;
+      }
+    } else {
+      // ---- bit packing ----------------------------------------------------------------------------------
+      const uint32_t ntok = s_misc[kMNTok];
+      for (uint32_t i = tid; i < (uint32_t)kStageBytes / 4; i += kLzThreads) s_stage[i] = 0;
+      __syncthreads();
+      if (tid == 0) {
+        SmemBitWriter bw{s_stage, 0};
+        if (mode == 1) {
+          bw.put(2, 3);  // BFINAL=0, BTYPE=01
+        } else {
+          bw.put(4, 3);  // BFINAL=0, BTYPE=10
+          bw.put(s_misc[kMHlit] - 257, 5);
+          bw.put(s_misc[kMHdist] - 1, 5);
+          bw.put(s_misc[kMHclen] - 4, 4);
+          for (uint32_t i = 0; i < s_misc[kMHclen]; i++) bw.put(s_cllen[cl_order((int)i)], 3);
+          for (uint32_t i = 0; i < s_misc[kMNRle]; i++) {
+            const uint32_t sym = s_rle[i] & 0xff, ex = s_rle[i] >> 8;
+            bw.put(s_clcode[sym], s_cllen[sym]);
+            bw.put(ex, cl_extra_bits(sym));
+          }
+        }
+      }
+      __syncthreads();
+      uint32_t bitpos = s_misc[kMHdrBits];  // absolute bit position inside the chunk's output
+      uint32_t flushed = 0;                 // bytes already written to global memory
+      for (uint32_t b0 = 0; b0 < ntok; b0 += kBatchTokens) {
+        // each thread encodes kTokPerThread consecutive tokens
+        uint64_t val[kTokPerThread];
+        uint32_t nb[kTokPerThread];
+        uint32_t mine = 0;
+#pragma unroll
+        for (int k = 0; k < kTokPerThread; k++) {
+          const uint32_t ti = b0 + tid * kTokPerThread + k;
+          uint64_t v = 0;
+          uint32_t n = 0;
+          if (ti < ntok) {
+            const uint32_t tok = tokens[ti];
+            if (tok & kTokMatch) {
+              const uint32_t len = ((tok >> 16) & 0xff) + 3, dist = (tok & 0x7fff) + 1;
+              const uint32_t lc = len_code(len), dc = dist_code(dist);
+              const uint32_t leb = len_extra_bits(lc), deb = dist_extra_bits(dc);
+              uint32_t lcd, lcl, dcd, dcl;
+              if (mode == 2) {
+                lcd = s_lcode[257 + lc]; lcl = s_llen[257 + lc]; dcd = s_dcode[dc]; dcl = s_dlen[dc];
+              } else {
+                const uint32_t sym = 257 + lc;
+                lcl = fixed_litlen_bits(sym);
+                lcd = bit_reverse(sym < 280 ? sym - 256 : 0xc0 + (sym - 280), (int)lcl);
+                dcl = 5;
+                dcd = bit_reverse(dc, 5);
+              }
+              v = lcd;
+              n = lcl;
+              v |= (uint64_t)(len - len_base(lc)) << n;
+              n += leb;
+              v |= (uint64_t)dcd << n;
+              n += dcl;
+              v |= (uint64_t)(dist - dist_base(dc)) << n;
+              n += deb;
+            } else {
+              if (mode == 2) {
+                v = s_lcode[tok];
+                n = s_llen[tok];
+              } else {
+                n = fixed_litlen_bits(tok);
+                const uint32_t code = tok < 144 ? 0x30 + tok : (tok < 256 ? 0x190 + (tok - 144) : tok - 256);
+                v = bit_reverse(code, (int)n);
+              }
+            }
+          }
+          val[k] = v;
+          nb[k] = n;
+          mine += n;
+        }
+        uint32_t batch_bits;
+        uint32_t off = block_exclusive_scan(mine, s_misc + kMScan, &batch_bits);
+        uint32_t o = bitpos - flushed * 8 + off;  // bit offset inside the window
+#pragma unroll
+        for (int k = 0; k < kTokPerThread; k++) {
+          if (nb[k]) {
+            const uint32_t w = o >> 5, s = o & 31;
+            const uint64_t v = val[k];
+            const uint32_t a0 = (uint32_t)(v << s);
+            const uint32_t a1 = s ? (uint32_t)(v >> (32 - s)) : (uint32_t)(v >> 32);
+            const uint32_t a2 = s ? (uint32_t)(v >> (64 - s)) : 0u;
+            if (a0) atomicOr(&s_stage[w], a0);
+            if (a1) atomicOr(&s_stage[w + 1], a1);
+            if (a2) atomicOr(&s_stage[w + 2], a2);
+            o += nb[k];
+          }
+        }
+        bitpos += batch_bits;
+        __syncthreads();
+        // flush whole bytes; carry the partial byte to the front of the window
+        const uint32_t whole = bitpos / 8 - flushed;
+        const bool last = b0 + kBatchTokens >= ntok;
+        if (!last) {
+          block_copy_unaligned(dst + flushed, reinterpret_cast<const uint8_t *>(s_stage), whole, tid, kLzThreads);
+          __syncthreads();
+          const uint32_t carry = reinterpret_cast<const uint8_t *>(s_stage)[whole];
+          __syncthreads();
+          for (uint32_t i = tid; i < (uint32_t)kStageBytes / 4; i += kLzThreads) s_stage[i] = 0;
+          __syncthreads();
+          if (tid == 0) s_stage[0] = (bitpos & 7) ? carry : 0;
+          flushed += whole;
+          __syncthreads();
+        } else {
+          // sync flush marker: stored block header (000), pad to byte, LEN=0000 NLEN=ffff
+          if (tid == 0) {
+            uint32_t p = bitpos - flushed * 8 + 3;  // three zero bits
+            p = (p + 7) & ~7u;
+            uint8_t *sb = reinterpret_cast<uint8_t *>(s_stage) + p / 8;
+            sb[0] = 0;
+            sb[1] = 0;
+            sb[2] = 0xff;
+            sb[3] = 0xff;
+          }
+          __syncthreads();
+          const uint32_t remain = chunk_bytes - flushed;
+          block_copy_unaligned(dst + flushed, reinterpret_cast<const uint8_t *>(s_stage), remain, tid, kLzThreads);
+        }
+      }
+    }
+    if (c == P.nchunks - 1 && P.write_terminator && tid == 0) {
+      dst[chunk_bytes] = 0x03;  // BFINAL=1, BTYPE=01, end-of-block
+      dst[chunk_bytes + 1] = 0x00;
+    }
+  }
+}
 
 }  // namespace dsg

@@ -61,7 +61,9 @@ enum { kTimPlan, kTimTar, kTimDeflate, kTimCrc, kTimGather, kTimTotal, kTimCount
 struct dsg_ctx {
   int device = 0;
   dsg_opts opts{};
-  cudaStream_t stream = nullptr;
+  cudaStream_t stream = nullptr;      // compute (and everything in the single-stream entry points)
+  cudaStream_t stream_in = nullptr;   // host -> device copies of the pipelined path
+  cudaStream_t stream_out = nullptr;  // device -> host copies of the pipelined path
   std::string err;
   dsg_stats stats{};
   std::mutex mu;
@@ -75,6 +77,8 @@ struct dsg_ctx {
   DevBuf crc_raw;
   // deflate
   DevBuf lz_scratch, chunk_sizes, chunk_offs;
+  // pipelined path: two slots each for the arena slice, the tar segment and the compressed segment
+  DevBuf slot_arena[2], slot_tar[2], slot_out[2], seg_ranges;
   Timer tim[kTimCount];
   uint64_t *h_scalars = nullptr;  // pinned mirror of `scalars`
   uint32_t launches = 0;
@@ -83,7 +87,8 @@ struct dsg_ctx {
 
 namespace {
 
-constexpr size_t kScalarWords = 16;  // u64 slots
+constexpr size_t kScalarWords = 16;   // u64 slots
+constexpr size_t kMaxSegSizes = 64;   // pinned ring of per-segment output sizes behind the scalar mirror
 // slot layout inside `scalars` (u64 units)
 enum { kSTotalBlocks = 0, kSPayload = 1, kSStatus = 2 /* DevStatus, 8 bytes */, kSCrc = 3 /* 3 x u32 in 2 slots */,
        kSDeflateBytes = 5, kSSpare = 6 };
@@ -283,14 +288,74 @@ int deflate_run(dsg_ctx *ctx, const uint8_t *d_in, uint64_t len, int level, uint
 // ---- LZ77 + Huffman path (level 6) -------------------------------------------------------------------------
 
 int lz_ctx_init(dsg_ctx *ctx) {
-  (void)ctx;
+  cudaError_t e = cudaFuncSetAttribute(lz_deflate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LzLayout::total);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return fail(ctx, DSG_E_CUDA, "cudaFuncSetAttribute(lz_deflate_kernel, %d bytes of shared memory): %s",
+                (int)LzLayout::total, cudaGetErrorString(e));
+  }
   return DSG_OK;
 }
 
+__global__ void lz_finish_empty_kernel(uint8_t *out, uint64_t *total_out, int write_terminator) {
+  if (threadIdx.x == 0) {
+    if (write_terminator) {
+      out[0] = 0x03;
+      out[1] = 0x00;
+    }
+    *total_out = write_terminator ? 2 : 0;
+  }
+}
+
+// Level-6 deflate of d_in[0,len) on `stream`: one persistent kernel. d_dict/dict_len: up to 32 KiB of the
+// member that precede d_in (previous pipeline segment). The produced size is written to *d_total (device),
+// a too-small d_out sets *d_error (device) to 1.
+int lz_launch(dsg_ctx *ctx, cudaStream_t stream, const uint8_t *d_in, uint64_t len, const uint8_t *d_dict,
+              uint32_t dict_len, uint8_t *d_out, uint64_t out_cap, uint64_t *d_total, uint32_t *d_error,
+              int write_terminator) {
+  if (len == 0) {
+    if (out_cap < 2 && write_terminator) return fail(ctx, DSG_E_CAPACITY, "deflate output needs 2 bytes");
+    lz_finish_empty_kernel<<<1, 32, 0, stream>>>(d_out, d_total, write_terminator);
+    LAUNCH_CHECK();
+    return DSG_OK;
+  }
+  const uint64_t nchunks64 = (len + kChunk - 1) / kChunk;
+  if (nchunks64 > 0xfffffff0ull) return fail(ctx, DSG_E_ARG, "input too large for one call");
+  const uint32_t nchunks = (uint32_t)nchunks64;
+  const uint32_t grid = std::min<uint32_t>(nchunks, (uint32_t)ctx->sm_count);
+  // scratch: look-back words (one per chunk) + ticket word, token slots (one per resident CTA)
+  CU(ctx->chunk_sizes.ensure(sizeof(unsigned long long) * (size_t)nchunks + 64));
+  CU(ctx->lz_scratch.ensure(sizeof(uint32_t) * (size_t)kTokSlotWords * ctx->sm_count));
+  CU(cudaMemsetAsync(ctx->chunk_sizes.p, 0, sizeof(unsigned long long) * (size_t)nchunks + 64, stream));
+  LzParams P;
+  P.in = d_in;
+  P.len = len;
+  P.dict = dict_len ? d_dict : nullptr;
+  P.dict_len = dict_len;
+  P.out = d_out;
+  P.out_cap = out_cap;
+  P.nchunks = nchunks;
+  unsigned long long *words = ctx->chunk_sizes.as<unsigned long long>();
+  P.state = words;
+  P.ticket = reinterpret_cast<uint32_t *>(words + nchunks);
+  P.error = d_error;
+  P.tok_scratch = ctx->lz_scratch.as<uint32_t>();
+  P.total_out = d_total;
+  P.write_terminator = write_terminator;
+  lz_deflate_kernel<<<grid, kLzThreads, LzLayout::total, stream>>>(P);
+  LAUNCH_CHECK();
+  return DSG_OK;
+}
+
+// Whole-buffer variant on the context's main stream: size -> scalars[kSDeflateBytes], error -> scalars[kSSpare]
+// (both read back with the other scalars after the caller's synchronisation).
 int lz_deflate_run(dsg_ctx *ctx, const uint8_t *d_in, uint64_t len, uint8_t *d_out, uint64_t out_cap,
                    uint64_t *out_len) {
-  (void)d_in; (void)len; (void)d_out; (void)out_cap; (void)out_len;
-  return fail(ctx, DSG_E_ARG, "level 6 kernels are not part of this build yet");
+  uint64_t *sc = ctx->scalars.as<uint64_t>();
+  *out_len = lz_deflate_bound(len);
+  CU(cudaMemsetAsync(sc + kSSpare, 0, sizeof(uint64_t), ctx->stream));
+  return lz_launch(ctx, ctx->stream, d_in, len, nullptr, 0, d_out, out_cap, sc + kSDeflateBytes,
+                   reinterpret_cast<uint32_t *>(sc + kSSpare), 1);
 }
 
 }  // namespace
@@ -361,7 +426,10 @@ int dsg_ctx_create(int device, const dsg_opts *opts, dsg_ctx **out) {
     if ((e = cudaEventCreate(&t.a)) != cudaSuccess) return bail(e, "event");
     if ((e = cudaEventCreate(&t.b)) != cudaSuccess) return bail(e, "event");
   }
-  if ((e = cudaMallocHost(reinterpret_cast<void **>(&ctx->h_scalars), sizeof(uint64_t) * kScalarWords)) != cudaSuccess)
+  if ((e = cudaStreamCreateWithFlags(&ctx->stream_in, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "stream");
+  if ((e = cudaStreamCreateWithFlags(&ctx->stream_out, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "stream");
+  if ((e = cudaMallocHost(reinterpret_cast<void **>(&ctx->h_scalars),
+                          sizeof(uint64_t) * (kScalarWords + kMaxSegSizes))) != cudaSuccess)
     return bail(e, "cudaMallocHost");
   if ((e = ctx->scalars.ensure(sizeof(uint64_t) * kScalarWords)) != cudaSuccess) return bail(e, "scalars");
   // CRC tables: built once on the host (2 x 5120 table entries), resident for the context's lifetime
@@ -389,7 +457,8 @@ void dsg_ctx_destroy(dsg_ctx *ctx) {
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   for (DevBuf *b : {&ctx->crc_tab, &ctx->crc_shift, &ctx->ent_blocks, &ctx->cta_sums, &ctx->ent_off, &ctx->scalars,
                     &ctx->d_entries, &ctx->d_strtab, &ctx->d_arena, &ctx->d_tar, &ctx->d_out, &ctx->crc_raw,
-                    &ctx->lz_scratch, &ctx->chunk_sizes, &ctx->chunk_offs})
+                    &ctx->lz_scratch, &ctx->chunk_sizes, &ctx->chunk_offs, &ctx->seg_ranges, &ctx->slot_arena[0],
+                    &ctx->slot_arena[1], &ctx->slot_tar[0], &ctx->slot_tar[1], &ctx->slot_out[0], &ctx->slot_out[1]})
     b->release();
   for (auto &t : ctx->tim) {
     if (t.a) cudaEventDestroy(t.a);
@@ -397,6 +466,8 @@ void dsg_ctx_destroy(dsg_ctx *ctx) {
   }
   if (ctx->h_scalars) cudaFreeHost(ctx->h_scalars);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  if (ctx->stream_in) cudaStreamDestroy(ctx->stream_in);
+  if (ctx->stream_out) cudaStreamDestroy(ctx->stream_out);
   cudaGetLastError();
   delete ctx;
 }
@@ -560,6 +631,9 @@ int dsg_dev_deflate(dsg_ctx *ctx, const uint8_t *d_in, size_t len, int level, ui
     CU(cudaMemcpy(ctx->h_scalars, ctx->scalars.p, sizeof(uint64_t) * kScalarWords, cudaMemcpyDeviceToHost));
     n = ctx->h_scalars[kSDeflateBytes];
     *out_len = (size_t)n;
+    if (ctx->h_scalars[kSSpare] != 0)
+      return fail(ctx, DSG_E_CAPACITY, "deflate output needs %llu bytes, capacity %llu", (unsigned long long)n,
+                  (unsigned long long)out_cap);
   }
   ctx->stats.tar_bytes = len;
   ctx->stats.out_bytes = n;
@@ -594,6 +668,9 @@ static int gzip_device(dsg_ctx *ctx, const uint8_t *d_in, uint64_t len, int leve
   CU(cudaStreamSynchronize(ctx->stream));
   *out_len = ctx->h_scalars[kSDeflateBytes] + 18;
   ctx->stats.crc32 = (uint32_t)ctx->h_scalars[kSCrc];
+  if (level != DSG_LEVEL_STORED && ctx->h_scalars[kSSpare] != 0)
+    return fail(ctx, DSG_E_CAPACITY, "gzip output needs %llu bytes, capacity %llu", (unsigned long long)*out_len,
+                (unsigned long long)out_cap);
   return DSG_OK;
 }
 
@@ -676,36 +753,239 @@ int dsg_pack_device(dsg_ctx *ctx, const dsg_entry *d_entries, size_t n, const ch
   return DSG_OK;
 }
 
-// Host buffers in, host buffer out.
+// Host buffers in, host buffer out, pipelined per segment of the tar stream:
+//   copy stream   : arena slice of segment i+1  host -> device
+//   compute stream: layout -> CRC32 -> deflate of segment i        (dictionary = tail of segment i-1)
+//   copy-back     : compressed bytes of segment i-1  device -> host, at the running output offset
+// Two device slots per buffer kind; the host only blocks on the per-segment size read-back.
 static int pack_host_pipelined(dsg_ctx *ctx, const dsg_entry *entries, size_t n, const char *strtab, size_t strtab_len,
                                const uint8_t *arena, size_t arena_len, bool gzip, uint8_t *out, size_t out_cap,
                                size_t *out_len) {
-  tic(ctx, kTimTotal);
+  constexpr int NS = 2;
+  cudaStream_t s_cmp = ctx->stream, s_in = ctx->stream_in, s_out = ctx->stream_out;
+  CU(cudaEventRecord(ctx->tim[kTimTotal].a, s_cmp));
+  // ---- manifest + plan ---------------------------------------------------------------------------------------
   CU(ctx->d_entries.ensure(sizeof(dsg_entry) * std::max<size_t>(n, 1)));
   CU(ctx->d_strtab.ensure(std::max<size_t>(strtab_len, 1)));
-  CU(ctx->d_arena.ensure(std::max<size_t>(arena_len, 1)));
-  if (n) CU(cudaMemcpyAsync(ctx->d_entries.p, entries, sizeof(dsg_entry) * n, cudaMemcpyHostToDevice, ctx->stream));
-  if (strtab_len) CU(cudaMemcpyAsync(ctx->d_strtab.p, strtab, strtab_len, cudaMemcpyHostToDevice, ctx->stream));
-  if (arena_len) CU(cudaMemcpyAsync(ctx->d_arena.p, arena, arena_len, cudaMemcpyHostToDevice, ctx->stream));
-  ctx->stats.h2d_bytes = sizeof(dsg_entry) * n + strtab_len + arena_len;
-  // size the device output from the plan (host-side helper is O(n); the device plan is authoritative)
-  uint64_t T = 0;
-  int rc = dsg_tar_size(entries, n, strtab, strtab_len, ctx->opts.flags, &T);
-  if (rc) return fail(ctx, rc, "manifest rejected: %s", dsg_strerror(rc));
-  const uint64_t need = gzip ? dsg_gzip_bound(T) : T;
-  CU(ctx->d_out.ensure(need + 64));
-  uint64_t produced = 0;
-  rc = pack_resident(ctx, ctx->d_entries.as<dsg_entry>(), n, ctx->d_strtab.as<char>(), strtab_len,
-                     ctx->d_arena.as<uint8_t>(), arena_len, gzip, ctx->d_out.as<uint8_t>(), need, &produced);
-  *out_len = (size_t)produced;
+  if (n) CU(cudaMemcpyAsync(ctx->d_entries.p, entries, sizeof(dsg_entry) * n, cudaMemcpyHostToDevice, s_cmp));
+  if (strtab_len) CU(cudaMemcpyAsync(ctx->d_strtab.p, strtab, strtab_len, cudaMemcpyHostToDevice, s_cmp));
+  uint64_t h2d = sizeof(dsg_entry) * n + strtab_len, d2h = 0;
+  const dsg_entry *d_entries = ctx->d_entries.as<dsg_entry>();
+  const char *d_strtab = ctx->d_strtab.as<char>();
+  uint64_t T = 0, P = 0;
+  int rc = tar_plan(ctx, d_entries, (uint32_t)n, d_strtab, strtab_len, arena_len, ctx->opts.flags, &T, &P);
   if (rc) return rc;
-  if (produced > out_cap) return fail(ctx, DSG_E_CAPACITY, "output needs %llu bytes", (unsigned long long)produced);
-  CU(cudaMemcpyAsync(out, ctx->d_out.p, produced, cudaMemcpyDeviceToHost, ctx->stream));
-  toc(ctx, kTimTotal);
-  CU(cudaStreamSynchronize(ctx->stream));
-  ctx->stats.d2h_bytes = produced;
-  ctx->stats.segments = 1;
+  ctx->stats.entries = n;
+  ctx->stats.payload_bytes = P;
+  ctx->stats.tar_bytes = T;
+  uint64_t S = ctx->opts.segment_bytes;
+  S = std::max<uint64_t>((S + kChunk - 1) / kChunk * kChunk, kChunk);
+  const uint32_t nseg = (uint32_t)std::max<uint64_t>((T + S - 1) / S, 1);
+  // per-segment arena ranges (device -> pinned host)
+  CU(ctx->seg_ranges.ensure(sizeof(uint64_t) * 3 * (size_t)nseg));
+  std::vector<uint64_t> h_rng(3 * (size_t)nseg);
+  unsigned long long *d_lo = ctx->seg_ranges.as<unsigned long long>(), *d_hi = d_lo + nseg;
+  uint64_t *d_segout = reinterpret_cast<uint64_t *>(d_hi + nseg);
+  CU(cudaMemsetAsync(d_lo, 0xff, sizeof(uint64_t) * nseg, s_cmp));
+  CU(cudaMemsetAsync(d_hi, 0, sizeof(uint64_t) * 2 * nseg, s_cmp));
+  if (n) {
+    tar_segment_ranges_kernel<<<(unsigned)((n + kPlanThreads - 1) / kPlanThreads), kPlanThreads, 0, s_cmp>>>(
+        d_entries, (uint32_t)n, ctx->ent_off.as<uint64_t>(), S, d_lo, d_hi);
+    LAUNCH_CHECK();
+  }
+  CU(cudaMemcpyAsync(h_rng.data(), d_lo, sizeof(uint64_t) * 2 * nseg, cudaMemcpyDeviceToHost, s_cmp));
+  CU(cudaStreamSynchronize(s_cmp));
+  uint64_t max_arena = 16;
+  for (uint32_t i = 0; i < nseg; i++) {
+    uint64_t lo = h_rng[i], hi = h_rng[nseg + i];
+    if (hi <= lo || lo == ~0ull) {
+      h_rng[i] = h_rng[nseg + i] = 0;
+      continue;
+    }
+    lo &= ~uint64_t(15);  // keeps the 16-byte alignment of payload starts relative to the slot base
+    h_rng[i] = lo;
+    max_arena = std::max(max_arena, hi - lo);
+  }
+  // ---- output framing (host memory: written directly) ----------------------------------------------------------
+  const uint64_t seg_out_cap = gzip ? lz_deflate_bound(std::min(S, std::max<uint64_t>(T, 1))) : 0;
+  size_t produced = 0;
+  if (gzip) {
+    if (out_cap < 18) {
+      *out_len = (size_t)dsg_gzip_bound(T);
+      return fail(ctx, DSG_E_CAPACITY, "gzip output needs at least 18 bytes");
+    }
+    static const uint8_t hdr[10] = {0x1f, 0x8b, 0x08, 0, 0, 0, 0, 0, 0, 0xff};  // compress/gzip Writer defaults
+    memcpy(out, hdr, 10);
+    produced = 10;
+  }
+  // ---- slots ---------------------------------------------------------------------------------------------------
+  for (int k = 0; k < NS; k++) {
+    CU(ctx->slot_arena[k].ensure(max_arena + 64));
+    if (gzip) {
+      CU(ctx->slot_tar[k].ensure(std::min(S, T) + 64));
+      CU(ctx->slot_out[k].ensure(seg_out_cap + 64));
+    } else {
+      CU(ctx->slot_tar[k].ensure(std::min(S, T) + 64));
+    }
+  }
+  if (gzip && ctx->opts.level != DSG_LEVEL_STORED) {
+    const uint64_t nch = (std::min(S, T) + kChunk - 1) / kChunk;
+    CU(ctx->chunk_sizes.ensure(sizeof(unsigned long long) * (size_t)nch + 64));
+    CU(ctx->lz_scratch.ensure(sizeof(uint32_t) * (size_t)kTokSlotWords * ctx->sm_count));
+  }
+  if (gzip) {
+    if ((rc = crc_reset(ctx))) return rc;
+  }
+  uint64_t *sc = ctx->scalars.as<uint64_t>();
+  CU(cudaMemsetAsync(sc + kSSpare, 0, sizeof(uint64_t), s_cmp));
+  std::vector<cudaEvent_t> ev_in(nseg), ev_cmp(nseg), ev_out(nseg), ev_t(2 * (size_t)nseg);
+  auto destroy_events = [&]() {
+    for (auto *v : {&ev_in, &ev_cmp, &ev_out, &ev_t})
+      for (cudaEvent_t e : *v)
+        if (e) cudaEventDestroy(e);
+  };
+  for (auto *v : {&ev_in, &ev_cmp, &ev_out})
+    for (auto &e : *v) {
+      e = nullptr;
+      if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) {
+        destroy_events();
+        return fail(ctx, DSG_E_CUDA, "cudaEventCreate failed");
+      }
+    }
+  for (auto &e : ev_t) {
+    e = nullptr;
+    if (cudaEventCreate(&e) != cudaSuccess) {
+      destroy_events();
+      return fail(ctx, DSG_E_CUDA, "cudaEventCreate failed");
+    }
+  }
+#define CUP(call)                                                                                          \
+  do {                                                                                                     \
+    cudaError_t e_ = (call);                                                                               \
+    if (e_ != cudaSuccess) {                                                                               \
+      cudaGetLastError();                                                                                  \
+      cudaDeviceSynchronize();                                                                             \
+      destroy_events();                                                                                    \
+      return fail(ctx, DSG_E_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__);   \
+    }                                                                                                      \
+  } while (0)
+
+  uint64_t *h_sizes = ctx->h_scalars + kScalarWords;  // pinned, kMaxSegSizes slots (ring)
+  int status = DSG_OK;
+  auto enqueue = [&](uint32_t i) -> int {
+    const int k = (int)(i % NS);
+    const uint64_t lo = (uint64_t)i * S, hi = std::min<uint64_t>(lo + S, T);
+    const uint64_t a_lo = h_rng[i], a_hi = h_rng[nseg + i];
+    // copy-in: slot k's previous user (segment i-NS) must have finished computing
+    if (i >= NS) CUP(cudaStreamWaitEvent(s_in, ev_cmp[i - NS], 0));
+    if (a_hi > a_lo) {
+      CUP(cudaMemcpyAsync(ctx->slot_arena[k].p, arena + a_lo, a_hi - a_lo, cudaMemcpyHostToDevice, s_in));
+      h2d += a_hi - a_lo;
+    }
+    CUP(cudaEventRecord(ev_in[i], s_in));
+    // compute
+    CUP(cudaStreamWaitEvent(s_cmp, ev_in[i], 0));
+    if (i >= NS) CUP(cudaStreamWaitEvent(s_cmp, ev_out[i - NS], 0));  // slot k's output has been copied back
+    CUP(cudaEventRecord(ev_t[2 * i], s_cmp));
+    uint8_t *d_seg = ctx->slot_tar[k].as<uint8_t>();
+    int r = tar_layout(ctx, d_entries, (uint32_t)n, d_strtab, ctx->slot_arena[k].as<uint8_t>(), a_lo, d_seg, lo, hi);
+    if (r) return r;
+    if (gzip) {
+      if ((r = crc_update(ctx, d_seg, hi - lo))) return r;
+      const bool last = i + 1 == nseg;
+      if (ctx->opts.level == DSG_LEVEL_STORED) {
+        const uint64_t nblocks = (hi - lo + kStoredMax - 1) / kStoredMax;
+        deflate_stored_kernel<<<(unsigned)std::max<uint64_t>(nblocks, 1), kStoredThreads, 0, s_cmp>>>(
+            d_seg, hi - lo, ctx->slot_out[k].as<uint8_t>(), last ? 1 : 0);
+        ctx->launches++;
+        set_u64_kernel<<<1, 1, 0, s_cmp>>>(d_segout + i, stored_deflate_size(hi - lo) - (last ? 0 : 2));
+        ctx->launches++;
+      } else {
+        const uint8_t *dict = nullptr;
+        uint32_t dict_len = 0;
+        if (i > 0) {  // tail of the previous segment, still resident in the other slot
+          dict_len = (uint32_t)std::min<uint64_t>(S, kDict);
+          dict = ctx->slot_tar[(i - 1) % NS].as<uint8_t>() + (S - dict_len);
+        }
+        r = lz_launch(ctx, s_cmp, d_seg, hi - lo, dict, dict_len, ctx->slot_out[k].as<uint8_t>(), seg_out_cap,
+                      d_segout + i, reinterpret_cast<uint32_t *>(sc + kSSpare), last ? 1 : 0);
+        if (r) return r;
+      }
+      CUP(cudaMemcpyAsync(&h_sizes[i % kMaxSegSizes], d_segout + i, sizeof(uint64_t), cudaMemcpyDeviceToHost, s_cmp));
+    }
+    CUP(cudaEventRecord(ev_t[2 * i + 1], s_cmp));
+    CUP(cudaEventRecord(ev_cmp[i], s_cmp));
+    return DSG_OK;
+  };
+  auto drain = [&](uint32_t i) -> int {
+    const int k = (int)(i % NS);
+    const uint64_t lo = (uint64_t)i * S, hi = std::min<uint64_t>(lo + S, T);
+    CUP(cudaEventSynchronize(ev_cmp[i]));
+    const uint64_t nbytes = gzip ? h_sizes[i % kMaxSegSizes] : hi - lo;
+    const uint64_t tail = gzip && i + 1 == nseg ? 8 : 0;
+    if (produced + nbytes + tail > out_cap) {
+      produced += nbytes + tail;
+      status = DSG_E_CAPACITY;
+      CUP(cudaEventRecord(ev_out[i], s_out));
+      return DSG_OK;
+    }
+    CUP(cudaStreamWaitEvent(s_out, ev_cmp[i], 0));
+    const void *src = gzip ? ctx->slot_out[k].p : ctx->slot_tar[k].p;
+    if (nbytes && status == DSG_OK) {
+      CUP(cudaMemcpyAsync(out + produced, src, nbytes, cudaMemcpyDeviceToHost, s_out));
+      d2h += nbytes;
+    }
+    produced += nbytes;
+    CUP(cudaEventRecord(ev_out[i], s_out));
+    return DSG_OK;
+  };
+  for (uint32_t i = 0; i < nseg && rc == DSG_OK; i++) {
+    rc = enqueue(i);
+    if (rc == DSG_OK && i >= 1) rc = drain(i - 1);
+  }
+  if (rc == DSG_OK) rc = drain(nseg - 1);
+  if (rc != DSG_OK) {
+    cudaDeviceSynchronize();
+    destroy_events();
+    return rc;
+  }
+  // trailer: CRC32 + ISIZE from the device-resident running state
+  CUP(cudaMemcpyAsync(ctx->h_scalars, sc, sizeof(uint64_t) * kScalarWords, cudaMemcpyDeviceToHost, s_cmp));
+  CUP(cudaStreamSynchronize(s_cmp));
+  CUP(cudaStreamSynchronize(s_out));
+  CUP(cudaEventRecord(ctx->tim[kTimTotal].b, s_out));
+  CUP(cudaEventSynchronize(ctx->tim[kTimTotal].b));
+  ctx->tim[kTimTotal].used = true;
+  float ms_cmp = 0.f;
+  for (uint32_t i = 0; i < nseg; i++) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, ev_t[2 * i], ev_t[2 * i + 1]) == cudaSuccess) ms_cmp += ms;
+  }
+  destroy_events();
+#undef CUP
+  DevStatus st;
+  memcpy(&st, &ctx->h_scalars[kSStatus], sizeof st);
+  if (st.code != 0) return fail(ctx, st.code, "entry %u: %s", st.entry, dsg_strerror(st.code));
+  if (gzip) {
+    const uint32_t *cs = reinterpret_cast<const uint32_t *>(&ctx->h_scalars[kSCrc]);
+    const uint32_t crc = cs[0], isize = cs[1];
+    ctx->stats.crc32 = crc;
+    if (status == DSG_OK) {
+      for (int b = 0; b < 4; b++) out[produced + b] = (uint8_t)(crc >> (8 * b));
+      for (int b = 0; b < 4; b++) out[produced + 4 + b] = (uint8_t)(isize >> (8 * b));
+    }
+    produced += 8;
+    if (ctx->h_scalars[kSSpare] != 0 && status == DSG_OK)
+      return fail(ctx, DSG_E_CUDA, "internal: segment output exceeded its bound");
+  }
+  *out_len = produced;
+  ctx->stats.h2d_bytes = h2d;
+  ctx->stats.d2h_bytes = d2h;
+  ctx->stats.segments = nseg;
   finish_stats(ctx, produced);
+  ctx->stats.ms_deflate = ms_cmp;  // pipelined mode: layout + CRC + deflate per segment, summed
+  if (status != DSG_OK) return fail(ctx, status, "output needs %llu bytes, capacity %llu", (unsigned long long)produced,
+                                    (unsigned long long)out_cap);
   return DSG_OK;
 }
 

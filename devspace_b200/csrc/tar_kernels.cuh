@@ -137,6 +137,28 @@ tar_offsets_kernel(const uint64_t *__restrict__ ent_blocks, uint32_t n, const ui
   if (i == n - 1) ent_off[n] = (excl + v) * kBlock;
 }
 
+// Arena byte range each pipeline segment of the stream needs: seg_lo[s] = min, seg_hi[s] = max over the
+// payload pieces falling into stream bytes [s*seg_bytes, (s+1)*seg_bytes). One thread per entry. The host
+// uploads exactly [seg_lo, seg_hi) before the segment's layout kernel (any arena order is correct; an
+// arena laid out in entry order gives minimal, non-overlapping uploads). seg_lo starts at ~0, seg_hi at 0.
+__global__ void __launch_bounds__(kPlanThreads)
+tar_segment_ranges_kernel(const dsg_entry *__restrict__ entries, uint32_t n, const uint64_t *__restrict__ ent_off,
+                          uint64_t seg_bytes, unsigned long long *__restrict__ seg_lo,
+                          unsigned long long *__restrict__ seg_hi) {
+  const uint32_t i = blockIdx.x * kPlanThreads + threadIdx.x;
+  if (i >= n) return;
+  const dsg_entry e = entries[i];
+  if (e.typeflag != '0' || e.size <= 0) return;
+  const uint64_t ps = ent_off[i + 1] - pad512((uint64_t)e.size);  // first payload byte in the stream
+  const uint64_t pe = ps + (uint64_t)e.size;
+  for (uint64_t s = ps / seg_bytes; s * seg_bytes < pe; s++) {
+    const uint64_t lo = ps > s * seg_bytes ? ps : s * seg_bytes;
+    const uint64_t hi = pe < (s + 1) * seg_bytes ? pe : (s + 1) * seg_bytes;
+    atomicMin(&seg_lo[s], (unsigned long long)(e.data_off + (lo - ps)));
+    atomicMax(&seg_hi[s], (unsigned long long)(e.data_off + (hi - ps)));
+  }
+}
+
 // ---- layout -----------------------------------------------------------------------------------------
 
 // Largest index e in [0, n] with ent_off[e] <= off  (ent_off is non-decreasing, ent_off[0] = 0).

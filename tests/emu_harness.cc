@@ -8,6 +8,8 @@
 
 #include <vector>
 
+#include "crc32.cuh"
+#include "deflate_lz.cuh"
 #include "tar_kernels.cuh"
 
 dim3 threadIdx, blockIdx, blockDim, gridDim;
@@ -55,6 +57,61 @@ int emu_tar_build(const dsg_entry *entries, uint32_t n, const char *strtab, uint
     return st.code;
   }
   return 0;
+}
+
+// Mirrors lz_deflate_run in dsgpack.cu: one launch of the persistent LZ77+Huffman kernel.
+int emu_lz_deflate(const uint8_t *in, uint64_t len, const uint8_t *dict, uint32_t dict_len, uint8_t *out,
+                   uint64_t cap, uint64_t *out_len, uint32_t grid) {
+  if (len == 0) {
+    out[0] = 3;
+    out[1] = 0;
+    *out_len = 2;
+    return 0;
+  }
+  const uint32_t nchunks = (uint32_t)((len + kChunk - 1) / kChunk);
+  if (grid == 0 || grid > nchunks) grid = nchunks;
+  std::vector<unsigned long long> state(nchunks + 8, 0);
+  std::vector<uint32_t> tok((size_t)grid * kTokSlotWords, 0xDEADBEEF);
+  uint32_t ticket = 0, error = 0;
+  uint64_t total = 0;
+  LzParams P;
+  P.in = in;
+  P.len = len;
+  P.dict = dict;
+  P.dict_len = dict_len;
+  P.out = out;
+  P.out_cap = cap;
+  P.nchunks = nchunks;
+  P.ticket = &ticket;
+  P.state = state.data();
+  P.tok_scratch = tok.data();
+  P.total_out = &total;
+  P.error = &error;
+  P.write_terminator = 1;
+  emu::launch(dim3(grid), dim3(kLzThreads), LzLayout::total, [&] { lz_deflate_kernel(P); });
+  *out_len = total;
+  return error ? DSG_E_CAPACITY : 0;
+}
+
+// Mirrors crc_update in dsgpack.cu.
+uint32_t emu_crc32(const uint8_t *buf, uint64_t len) {
+  std::vector<uint32_t> tab(kCrcTables * 256), shift(kCrcShiftEntries);
+  crc_build_tables(tab.data(), shift.data(), (uint64_t)kCrcThreads * 16);
+  uint32_t state[4] = {0, 0, 0, 0};
+  if (len == 0) return 0;
+  uint32_t head = (uint32_t)((16 - ((uintptr_t)buf & 15)) & 15);
+  if (head > len) head = (uint32_t)len;
+  const uint64_t body = (len - head) & ~uint64_t(15);
+  const uint32_t tail = (uint32_t)(len - head - body);
+  const uint32_t ntiles = (uint32_t)((body + kCrcTileBytes - 1) / kCrcTileBytes);
+  std::vector<uint32_t> raw(ntiles + 1);
+  if (ntiles)
+    emu::launch(dim3(ntiles), dim3(kCrcThreads), 0, [&] {
+      crc_tiles_kernel(reinterpret_cast<const uint4 *>(buf + head), body / 16, tab.data(), shift.data(), raw.data());
+    });
+  emu::launch(dim3(1), dim3(256), 0,
+              [&] { crc_join_kernel(raw.data(), ntiles, body, buf, head, buf + head + body, tail, state); });
+  return state[0];
 }
 
 }  // extern "C"

@@ -1,0 +1,108 @@
+"""CPU: the LZ77 + Huffman deflate kernel and the CRC kernels (devspace_b200/csrc/deflate_lz.cuh, crc32.cuh)
+compiled for the SIMT emulator. Checks kernel LOGIC without a GPU: the stream must inflate to the input with a
+stock decoder (zlib) and stay close to zlib level 6 in size. Inputs are small: the emulator runs every CUDA
+thread as a fiber. The real parity tests are the -m gpu ones."""
+import ctypes
+import zlib
+
+import numpy as np
+import pytest
+
+import helpers
+
+lib = None
+
+
+def _lib():
+    global lib
+    if lib is None:
+        lib = helpers.emu_lib()
+        lib.emu_crc32.restype = ctypes.c_uint32
+    return lib
+
+
+def emu_deflate(data: bytes, grid: int = 0, dict_: bytes = b""):
+    L = _lib()
+    a = np.frombuffer(data, np.uint8)
+    d = np.frombuffer(dict_, np.uint8)
+    cap = len(data) + 10 * ((len(data) + 65535) // 65536) + 128
+    out = np.zeros(cap, np.uint8)
+    n = ctypes.c_uint64()
+    rc = L.emu_lz_deflate(ctypes.c_void_p(a.ctypes.data if len(data) else None), ctypes.c_uint64(len(data)),
+                          ctypes.c_void_p(d.ctypes.data if len(dict_) else None), ctypes.c_uint32(len(dict_)),
+                          ctypes.c_void_p(out.ctypes.data), ctypes.c_uint64(cap), ctypes.byref(n), ctypes.c_uint32(grid))
+    assert rc == 0
+    return out[: n.value].tobytes()
+
+
+def zlib6(data: bytes) -> int:
+    c = zlib.compressobj(6, zlib.DEFLATED, -15, 8)
+    return len(c.compress(data) + c.flush())
+
+
+def realistic_text(n: int, seed: int) -> bytes:
+    from devspace_b200 import synth
+    return synth.text_like(n, seed).numpy().tobytes()
+
+
+CASES = {
+    "empty": b"",
+    "3B": b"abc",
+    "rep600": b"abcabcabcabc" * 50,
+    "zeros_70k": b"\0" * 70_000,                      # two chunks, maximal matches, distance 1
+    "rand_66k": helpers.rng_bytes(2, 66_000),          # stored chunks (two stored blocks for a full chunk)
+    "text_20k": helpers.text_bytes(1, 20_000),
+    "text_140k": realistic_text(140_000, 3),           # three chunks: dictionary carried across chunk boundaries
+    "mixed_100k": realistic_text(30_000, 4) + helpers.rng_bytes(5, 40_000) + b"\0" * 30_000,
+    "chunk_exact": realistic_text(65_536, 6),
+    "chunk_plus1": realistic_text(65_537, 7),
+    "tile_edges": (b"0123456789abcdef" * 600)[:8192 - 3] + helpers.rng_bytes(8, 7) + b"0123456789abcdef" * 700,
+}
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_emulated_deflate_inflates_with_zlib(name):
+    data = CASES[name]
+    z = emu_deflate(data)
+    assert zlib.decompress(z, -15) == data
+    assert z[-2:] == b"\x03\x00"                                   # final empty fixed block
+    if name.startswith("text") or name.startswith("chunk"):
+        assert len(z) <= 1.12 * zlib6(data)                        # sanity only; the 3 % bar is judged on the GPU
+    if name == "zeros_70k":
+        assert len(z) < 400                                        # ~150 B per 64 KiB chunk: tables + sync marker
+
+
+def test_emulated_deflate_persistent_grid_and_dictionary():
+    data = realistic_text(200_000, 9)
+    one = emu_deflate(data, grid=1)            # one CTA walks all four chunks through the ticket counter
+    two = emu_deflate(data, grid=3)
+    assert one == two                           # chunk outputs do not depend on which CTA ran them
+    assert zlib.decompress(one, -15) == data
+    # a segment that continues a member: the previous 32 KiB are handed in as the dictionary
+    head, tail = data[:100_000], data[100_000:]
+    z = emu_deflate(tail, dict_=head[-32768:])
+    d = zlib.decompressobj(-15, zdict=head[-32768:])
+    assert d.decompress(z) == tail
+    assert len(z) < len(emu_deflate(tail))      # the dictionary is really used
+
+
+def test_emulated_incompressible_is_stored_with_small_overhead():
+    data = helpers.rng_bytes(10, 131_072)
+    z = emu_deflate(data)
+    assert zlib.decompress(z, -15) == data
+    assert len(z) == len(data) + 2 * 10 + 2     # two stored blocks per 64 KiB chunk + terminator
+
+
+@pytest.mark.parametrize("n", [0, 1, 15, 16, 17, 4095, 131072, 131073, 300_001])
+def test_emulated_crc32(n):
+    data = helpers.rng_bytes(n + 1, n)
+    a = np.frombuffer(data, np.uint8)
+    got = _lib().emu_crc32(ctypes.c_void_p(a.ctypes.data if n else None), ctypes.c_uint64(n))
+    assert got == zlib.crc32(data)
+
+
+def test_emulated_crc32_unaligned_pointer():
+    data = np.frombuffer(helpers.rng_bytes(3, 200_000), np.uint8)
+    for off in (1, 5, 9, 13):
+        got = _lib().emu_crc32(ctypes.c_void_p(data.ctypes.data + off), ctypes.c_uint64(150_000))
+        assert got == zlib.crc32(data[off:off + 150_000].tobytes())

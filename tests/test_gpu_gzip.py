@@ -2,6 +2,7 @@
 Judged equalities: gunzip(out) == oracle tar stream byte for byte; stock decoders accept the
 output; compressed size within 3 % of the oracle's zlib level-6 size (level 6 only)."""
 import gzip
+import os
 import shutil
 import struct
 import subprocess
@@ -92,3 +93,118 @@ def test_pack_device_resident_matches_host_path(packer0):
     finally:
         dm.free()
         d_out.free()
+
+
+# ---- level 6: LZ77 + dynamic Huffman kernels ---------------------------------------------------------------------
+
+@pytest.fixture(scope="module")
+def packer6():
+    from devspace_b200.pack import Packer
+    p = Packer(level=6)
+    yield p
+    p.close()
+
+
+def _zlib6(data: bytes) -> int:
+    c = zlib.compressobj(6, zlib.DEFLATED, -15, 8)
+    return len(c.compress(data) + c.flush())
+
+
+@pytest.mark.parametrize("name", sorted(BUFS))
+def test_level6_deflate_roundtrip(packer6, name):
+    data = BUFS[name]
+    raw = packer6.deflate(data, level=6)
+    assert zlib.decompress(raw, -15) == data
+    assert raw[-2:] == b"\x03\x00"
+    g = packer6.deflate(data, level=6, gzip=True)
+    assert g[:10] == bytes.fromhex("1f8b08000000000000ff")
+    assert struct.unpack("<II", g[-8:]) == (zlib.crc32(data), len(data) & 0xFFFFFFFF)
+    assert gzip.decompress(g) == data
+    assert len(raw) <= len(data) + 10 * ((len(data) + 65535) // 65536) + 2       # never worse than stored chunks
+
+
+def test_level6_size_within_3pct_of_zlib6_on_realistic_data(packer6):
+    """Judged equality (3): compressed size <= 1.03 x the oracle's zlib level-6 size."""
+    from devspace_b200 import synth
+    for name, data in (("js_like_text", synth.text_like(6_000_000, 21).numpy().tobytes()),
+                       ("elf_like_binary", synth.binary_like(6_000_000, 22).numpy().tobytes()),
+                       ("c1_quickstart", gzip.decompress(open(os.path.join(os.path.dirname(__file__), "golden",
+                                                                           "c1_quickstart.tgz"), "rb").read()))):
+        raw = packer6.deflate(data, level=6)
+        assert zlib.decompress(raw, -15) == data
+        ref = _zlib6(data)
+        assert len(raw) <= 1.03 * ref, (name, len(raw), ref, len(raw) / ref)
+
+
+@pytest.mark.parametrize("name", ["util_test_tree", "empty_archive", "mixed_tree", "name_5000", "pax_multi",
+                                  "single_empty_file"])
+def test_level6_pack_gunzips_to_oracle_tar(packer6, name, tmp_path):
+    es = SUITE[name]
+    out = packer6.pack(from_entries(es))
+    ref = oracle.tar_stream(es)
+    assert gzip.decompress(out) == ref                      # judged equality (1): bit-exact tar stream
+    st = packer6.stats()
+    assert st["crc32"] == zlib.crc32(ref) and st["tar_bytes"] == len(ref) and st["kernel_launches"] > 0
+    if shutil.which("tar") and name != "name_5000":        # judged equality (2): stock decoders accept it
+        p = tmp_path / "a.tgz"
+        p.write_bytes(out)
+        r = subprocess.run(["tar", "tzf", str(p)], capture_output=True)
+        assert r.returncode == 0 and r.stderr == b"" and len(r.stdout.split(b"\n")) - 1 == len(es)
+        assert subprocess.run(["gzip", "-t", str(p)], capture_output=True).returncode == 0
+
+
+def test_level6_pipeline_segments_share_one_member(tmp_path):
+    """64 KiB segments: 15 segments for mixed_tree; the dictionary crosses segment boundaries, the CRC is
+    folded across segments, and the result is still one gzip member equal to the oracle's tar stream."""
+    from devspace_b200.pack import Packer
+    es = SUITE["mixed_tree"]
+    ref = oracle.tar_stream(es)
+    with Packer(level=6, segment_bytes=65536) as p:
+        out = p.pack(from_entries(es))
+        st = p.stats()
+    assert st["segments"] == (len(ref) + 65535) // 65536 and st["segments"] > 8
+    assert gzip.decompress(out) == ref
+    with Packer(level=6) as p:
+        whole = p.pack(from_entries(es))
+    assert abs(len(out) - len(whole)) <= 0.01 * len(whole)            # segmentation costs (almost) nothing
+    with Packer(level=0, segment_bytes=131072) as p:
+        assert gzip.decompress(p.pack(from_entries(es))) == ref
+        assert p.pack(from_entries(es), tar_only=True) == ref
+
+
+def test_level6_small_trees_size_vs_oracle(packer6):
+    from devspace_b200 import synth
+    for man in (synth.tree_c2(3000, 12_000_000), synth.tree_c4(2, 6 << 20)):
+        out = packer6.pack(man)
+        tar = gzip.decompress(out)
+        # the tar stream itself is checked against the oracle through the generic path
+        es = [oracle.Entry(name=man.name(i), size=int(e["size"]), mtime_sec=int(e["mtime_sec"]), mode=int(e["mode"]),
+                           uid=1000, gid=1000, uname=b"dev", gname=b"dev", data=man.payload(i))
+              for i, e in enumerate(man.entries)]
+        assert tar == oracle.tar_stream(es)
+        ref = len(oracle.gzip_pack(tar, 6))
+        assert len(out) <= 1.03 * ref, (len(out), ref)
+
+
+def test_level6_pack_device_and_capacity_error(packer6):
+    from devspace_b200._lib import DsgError
+    from devspace_b200.pack import DeviceBuffer, DeviceManifest
+    es = SUITE["mixed_tree"]
+    man = from_entries(es)
+    dm = DeviceManifest(packer6, man)
+    d_out = DeviceBuffer(packer6, packer6.gzip_bound(packer6.tar_size(man)) + 64)
+    small = DeviceBuffer(packer6, 4096)
+    try:
+        n = packer6.pack_device(dm, d_out)
+        assert gzip.decompress(d_out.download(n).tobytes()) == oracle.tar_stream(es)
+        with pytest.raises(DsgError) as ei:
+            packer6.pack_device(dm, small)
+        assert ei.value.status == -5
+        out = np.empty(1000, np.uint8)
+        with pytest.raises(DsgError) as ei:
+            packer6.pack_into(man, out)
+        assert ei.value.status == -5
+    finally:
+        dm.free()
+        d_out.free()
+        small.free()
