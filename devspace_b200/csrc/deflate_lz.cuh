@@ -88,7 +88,7 @@ struct LzLayout {
 };
 static_assert(LzLayout::prev % 16 == 0 && LzLayout::head % 16 == 0 && LzLayout::mlen % 16 == 0, "alignment");
 static_assert(kTile + 2 * kTile >= kStageBytes, "bit-packing window must fit in the match arrays");
-static_assert(sizeof(HuffScratch) * 2 + 512 <= 4 * kHashSize, "Huffman scratch must fit in the head table");
+static_assert(sizeof(HuffScratch) * 2 + 512 + 4 * 80 <= 4 * kHashSize, "Huffman scratch must fit in the head table");
 static_assert(LzLayout::total <= 227 * 1024, "shared memory budget");
 static_assert(kMaxDist % 16 == 0 && kLook % 16 == 0, "ring loads move 16-byte granules");
 
@@ -111,7 +111,10 @@ struct LzParams {
   uint64_t *total_out;        // deflate bytes produced by this launch (written by the last chunk's CTA)
   uint32_t *error;            // set to 1 when out_cap is too small
   int write_terminator;       // append the final empty fixed block (03 00)
+  unsigned long long *prof;   // optional: cycles per phase, summed over CTAs (thread 0's clock64 deltas)
 };
+
+enum { kProfLoad = 0, kProfInsert, kProfSearch, kProfParse, kProfEmit, kProfHuff, kProfSizes, kProfPack, kProfCount };
 
 DSG_D uint32_t ring_slot(int rp /* chunk-relative position, >= -kDict */) {
   uint32_t x = (uint32_t)(rp + kDict);
@@ -209,76 +212,161 @@ DSG_D void load_ring(uint8_t *s_data, const LzParams &P, int64_t cs, int rp0, in
   }
 }
 
-// Inserts positions [rp0, rp1) into the hash chains, 512 consecutive positions per round.
-DSG_D void insert_positions(const uint8_t *s_data, uint16_t *s_prev, uint32_t *s_head, int rp0, int rp1) {
+// Inserts positions [rp0, rp1) into the hash chains in EXACT stream order (nearest candidate first), 512
+// positions per round, one per thread. Inside a round the threads race, so a thread does a lock-free sorted
+// insertion: it walks past entries of its own round that lie LATER in the stream (at most a handful, they can
+// only be ahead by < 512 positions) and links itself below them with a compare-and-swap on the link it came
+// through (32-bit CAS on the head table, 16-bit CAS on a prev[] entry). Exact order matters: chains that are
+// only ordered per round cost 1-3 % of compressed size (tools/lzmodel.cc, SCRAMBLE=512).
+// Positions in the interior of a byte run (the five bytes p-1..p+3 are equal) are not inserted: every one of
+// them would land in the same bucket (quadratic walks, useless candidates); the search gives them the
+// distance-1 candidate directly. They still get a chain start (prev[] = head after the round).
+DSG_D void insert_positions(const uint8_t *s_data, uint16_t *s_prev, uint32_t *s_head, int rp0, int rp1, int lo_rp) {
+  unsigned short *prev16 = reinterpret_cast<unsigned short *>(s_prev);
   for (int base = rp0; base < rp1; base += kLzThreads) {
     const int rp = base + (int)threadIdx.x;
-    if (rp < rp1) {
-      const uint32_t slot = ring_slot(rp);
-      const uint32_t h = hash4(load4(s_data + slot));
-      const uint32_t old = atomicExch(&s_head[h], slot);
-      s_prev[slot] = (uint16_t)old;
+    const bool on = rp < rp1;
+    uint32_t slot = 0, h = 0;
+    bool interior = false;
+    if (on) {
+      slot = ring_slot(rp);
+      const uint32_t v = load4(s_data + slot);
+      h = hash4(v);
+      interior = rp > lo_rp && v == load4(s_data + ring_slot(rp - 1));
+      if (!interior) {
+        bool at_head = true;
+        uint32_t holder = h;  // the link we would be written into: head[h], or prev[holder]
+        int walked = 0;
+        for (;;) {
+          const uint32_t nxt = at_head ? s_head[holder] : (uint32_t)prev16[holder];
+          if (nxt != kNil && ++walked < 2 * kLzThreads) {  // the bound only guards against stale links
+            int fwd = (int)nxt - (int)slot;
+            if (fwd < 0) fwd += kRing;
+            if (fwd > 0 && fwd < kLzThreads) {  // an entry of this round that is later in the stream
+              at_head = false;
+              holder = nxt;
+              continue;
+            }
+          }
+          prev16[slot] = (unsigned short)nxt;
+          __threadfence_block();  // our own link is visible before we become reachable
+          const uint32_t seen = at_head ? atomicCAS(&s_head[holder], nxt, slot)
+                                        : (uint32_t)atomicCAS(&prev16[holder], (unsigned short)nxt, (unsigned short)slot);
+          if (seen == nxt) break;  // else somebody linked in first: look at the same link again
+        }
+      }
     }
-    __syncthreads();  // rounds are ordered; inside a round the order of equal hashes is arbitrary
+    __syncthreads();
+    if (on && interior) prev16[slot] = (unsigned short)s_head[h];
+    __syncthreads();  // the next round must not move the heads under the readers above
   }
 }
 
 // Longest match for every position of the tile. tile_rp = chunk-relative position of the tile start,
 // chunk_len = bytes in this chunk, lo_rp = lowest chunk-relative position holding real data (-dictionary).
+// One thread owns a run of kRun consecutive positions; a position inherits (len-1, dist) from its
+// predecessor. The loop is flattened: every iteration performs ONE chain step (or finishes a position and
+// sets up the next), so the lanes of a warp do not wait for the lane with the longest chain at each position.
 DSG_D void search_tile(const uint8_t *s_data, const uint16_t *s_prev, uint8_t *s_mlen, uint16_t *s_mdist, int tile_rp,
                        int chunk_len, int lo_rp) {
   const int t0 = (int)threadIdx.x * kRun;
   int inh_len = 0, inh_dist = 0;
-#pragma unroll 1
-  for (int j = 0; j < kRun; j++) {
-    const int tp = t0 + j;      // tile-relative
-    const int rp = tile_rp + tp;  // chunk-relative
-    int best = 0, bdist = 0;
-    const int maxlen = chunk_len - rp < kMaxMatch ? chunk_len - rp : kMaxMatch;
-    if (maxlen >= kMinMatch) {
-      if (inh_len > kMinMatch) {
-        best = inh_len - 1;
-        bdist = inh_dist;
-        if (best > maxlen) best = maxlen;
-      }
-      int depth = kDepth;
-      if (best >= kNice) depth = 0;
-      else if (best >= kGood) depth = kDepth / 4;
-      const uint32_t slot = ring_slot(rp);
-      const uint8_t *a = s_data + slot;
-      const int max_back = rp - lo_rp < kMaxDist ? rp - lo_rp : kMaxDist;  // farthest usable distance
-      uint32_t q = s_prev[slot];
-      uint8_t a_hi = a[best], a_lo = best ? a[best - 1] : 0;
-      while (depth-- > 0 && q != kNil) {
-        int d = (int)slot - (int)q;
-        if (d <= 0) d += kRing;
-        if (d > max_back) {
-          if (d > kRing - 2 * kLzThreads) {  // inserted in the same round but later in the stream: skip
-            q = s_prev[q];
-            continue;
-          }
-          break;  // outside the window (or a stale link)
+  int j = 0;
+  bool setup = true;
+  int tp = 0, maxlen = 0, best = 0, bdist = 0, depth = 0, max_back = 0, last_d = 0;
+  uint32_t slot = 0, q = kNil, aw = 0, v_prev = 0;
+  int skips = 0;
+  const uint8_t *a = s_data;
+  while (j < kRun) {
+    if (setup) {
+      setup = false;
+      tp = t0 + j;
+      const int rp = tile_rp + tp;
+      maxlen = chunk_len - rp < kMaxMatch ? chunk_len - rp : kMaxMatch;
+      best = 0;
+      bdist = 0;
+      depth = 0;
+      q = kNil;
+      last_d = 0;
+      if (maxlen >= kMinMatch) {
+        if (inh_len > kMinMatch) {
+          best = inh_len - 1 < maxlen ? inh_len - 1 : maxlen;
+          bdist = inh_dist;
         }
+        slot = ring_slot(rp);
+        a = s_data + slot;
+        max_back = rp - lo_rp < kMaxDist ? rp - lo_rp : kMaxDist;
+        const uint32_t v = load4(a);
+        if (j == 0) v_prev = max_back > 0 ? load4(s_data + ring_slot(rp - 1)) : ~v;
+        if (v == v_prev && max_back > 0 && best < kNice) {
+          // interior of a byte run: the distance-1 candidate (never in the chains, see insert_positions)
+          const uint8_t *b1 = s_data + ring_slot(rp - 1);
+          int l = 4;
+          while (l < maxlen) {
+            const uint32_t x = load4(a + l) ^ load4(b1 + l);
+            if (x) {
+              l += (__ffs((int)x) - 1) >> 3;
+              break;
+            }
+            l += 4;
+          }
+          if (l > maxlen) l = maxlen;
+          if (l > best || (l == best && bdist > 1)) {
+            best = l;
+            bdist = 1;
+          }
+        }
+        v_prev = v;
+        depth = best >= kNice ? 0 : (best >= kGood ? kDepth / 4 : kDepth);
+        q = s_prev[slot];
+        skips = 0;
+        aw = load4(a + (best >= 3 ? best - 3 : 0));  // the four bytes a better match has to reproduce last
+      }
+    }
+    if (depth > 0 && q != kNil) {
+      depth--;
+      int d = (int)slot - (int)q;
+      if (d <= 0) d += kRing;
+      if (d > kRing - kLzThreads && skips < 64) {
+        // chain start of a run-interior position may be an entry of the same round that is later in the stream
+        skips++;
+        depth++;
+        q = s_prev[q];
+      } else if (d > max_back || d <= last_d) {
+        q = kNil;  // left the window, or a stale link (chains are in exact stream order: distances grow)
+      } else {
+        last_d = d;
         const uint8_t *b = s_data + q;
-        if (b[best] == a_hi && (best == 0 || b[best - 1] == a_lo)) {
+        const uint32_t qn = s_prev[q];  // next link, fetched before the compare so that its latency overlaps
+        if (load4(b + (best >= 3 ? best - 3 : 0)) == aw) {
           int l = 0;
-          while (l < maxlen && a[l] == b[l]) l++;
-          if (l >= kMinMatch && (l > best || (l == best && d < bdist))) {
+          while (l < maxlen) {
+            const uint32_t x = load4(a + l) ^ load4(b + l);
+            if (x) {
+              l += (__ffs((int)x) - 1) >> 3;
+              break;
+            }
+            l += 4;
+          }
+          if (l > maxlen) l = maxlen;
+          if (l >= kMinMatch && l > best) {
             best = l;
             bdist = d;
-            if (l >= kNice || l >= maxlen) break;
-            a_hi = a[best];
-            a_lo = a[best - 1];
+            if (l >= kNice || l >= maxlen) depth = 0;
+            else aw = load4(a + best - 3);
           }
         }
-        q = s_prev[q];
+        q = qn;
       }
+    } else {
       if (best < kMinMatch) best = 0;
+      s_mlen[tp] = (uint8_t)(best ? best - 3 : 0);  // 0 = no match, else len-3 in 1..255
+      s_mdist[tp] = (uint16_t)bdist;
+      inh_len = best;
+      inh_dist = bdist;
+      j++;
+      setup = true;
     }
-    s_mlen[tp] = (uint8_t)(best ? best - 3 : 0);  // 0 = no match, else len-3 in 1..255
-    s_mdist[tp] = (uint16_t)bdist;
-    inh_len = best;
-    inh_dist = bdist;
   }
 }
 
@@ -309,11 +397,29 @@ DSG_D int parse_tile_warp0(const uint8_t *s_mlen, uint32_t *s_bitmap, int start,
   const int sub_hi = (sub_lo + kSub < tile_len) ? sub_lo + kSub : tile_len;
   uint32_t *bm = s_bitmap;  // each lane owns words [lane*8, lane*8+8)
   for (int w = 0; w < kSub / 32; w++) bm[lane * (kSub / 32) + w] = 0;
-  // speculative walk from the sub-range start (lane 0: from the true start)
+  // speculative walk from the sub-range start (lane 0: from the true start). The current bitmap word is kept
+  // in a register; four literals in a row (the common case in incompressible data) are taken in one step.
   int p = lane == 0 ? start : sub_lo;
-  while (p < sub_hi) {
-    bm[p >> 5] |= 1u << (p & 31);
-    p += parse_step(s_mlen, p, tile_len);
+  {
+    int widx = p >> 5;
+    uint32_t cur = 0;
+    while (p < sub_hi) {
+      const int wi = p >> 5;
+      if (wi != widx) {
+        bm[widx] = cur;
+        widx = wi;
+        cur = 0;
+      }
+      if ((p & 3) == 0 && p + 4 <= sub_hi && p + 4 < tile_len &&
+          *reinterpret_cast<const uint32_t *>(s_mlen + p) == 0u) {
+        cur |= 0xfu << (p & 31);
+        p += 4;
+        continue;
+      }
+      cur |= 1u << (p & 31);
+      p += parse_step(s_mlen, p, tile_len);
+    }
+    if (cur) bm[widx] = cur;
   }
   const int exit_p = p;  // first token start at or beyond the end of the sub-range
   __syncwarp();
@@ -355,6 +461,116 @@ DSG_D int parse_tile_warp0(const uint8_t *s_mlen, uint32_t *s_bitmap, int start,
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// CTA-cooperative Huffman construction (literal/length and distance trees side by side)
+// ---------------------------------------------------------------------------------------------------------
+// Thread roles: the literal/length tree uses threads [0, 286), the distance tree threads [288, 318); the two
+// serial merges run on thread 0 and thread 288 (different warps). Every step is followed by a barrier in the
+// caller-visible function below, so all threads of the CTA must call it.
+struct HuffJob {
+  const uint32_t *freq;  // n frequencies
+  uint8_t *lens;         // n code lengths out
+  uint16_t *codes;       // n bit-reversed canonical codes out
+  HuffScratch *S;
+  uint32_t *ctrl;        // [0] m (used symbols), [1] max depth, [2] max used symbol, [3..19] bl_count, [20..36] next_code
+  int n;
+  int t0;                // first thread of this job
+};
+
+DSG_D void huff_jobs_build(const HuffJob &A, const HuffJob &B) {
+  const int tid = (int)threadIdx.x;
+  const bool inA = tid >= A.t0 && tid < A.t0 + A.n;
+  const bool inB = tid >= B.t0 && tid < B.t0 + B.n;
+  const HuffJob &J = inB ? B : A;
+  const bool active = inA || inB;
+  const int i = tid - J.t0;
+  // step 0: clear control words and lengths
+  if (active) {
+    J.lens[i] = 0;
+    for (int k = i; k < 40; k += J.n) J.ctrl[k] = 0;
+  }
+  __syncthreads();
+  // step 1: rank sort by (frequency, symbol) among the used symbols
+  uint32_t f = 0;
+  if (active) {
+    f = J.freq[i];
+    if (f) {
+      int rank = 0;
+      for (int j = 0; j < J.n; j++) {
+        const uint32_t g = J.freq[j];
+        rank += (g != 0 && (g < f || (g == f && j < i))) ? 1 : 0;
+      }
+      J.S->order[rank] = (uint16_t)i;
+      J.S->weight[rank] = f;
+      atomicAdd(&J.ctrl[0], 1u);
+      atomicMax(&J.ctrl[2], (uint32_t)i);
+    }
+  }
+  __syncthreads();
+  // step 2: serial two-queue merge (one thread per tree)
+  if (active && i == 0) {
+    const int m = (int)J.ctrl[0];
+    if (m >= 2) J.ctrl[37] = (uint32_t)huff_merge_sorted(*J.S, m);
+  }
+  __syncthreads();
+  // step 3: leaf depths by walking up the parent links
+  if (active) {
+    const int m = (int)J.ctrl[0];
+    if (m >= 2 && i < m) {
+      const int root = (int)J.ctrl[37];
+      int node = i, d = 0;
+      while (node != root) {
+        node = J.S->parent[node];
+        d++;
+      }
+      atomicMax(&J.ctrl[1], (uint32_t)d);
+      J.lens[J.S->order[i]] = (uint8_t)d;  // final when no code exceeds the limit (checked next)
+    }
+  }
+  __syncthreads();
+  // step 4: degenerate trees and the (rare) length-limit repair, serial
+  if (active && i == 0) {
+    const int m = (int)J.ctrl[0];
+    if (m == 0) {
+      J.lens[0] = 1;
+      J.lens[1] = 1;
+      J.ctrl[2] = 1;
+    } else if (m == 1) {
+      const int sy = J.S->order[0];
+      const int other = sy == 0 ? 1 : 0;
+      J.lens[sy] = 1;
+      J.lens[other] = 1;
+      J.ctrl[2] = (uint32_t)(sy > other ? sy : other);
+    } else if (J.ctrl[1] > (uint32_t)kMaxBits) {
+      huff_lengths_from_tree(*J.S, m, (int)J.ctrl[37], kMaxBits, J.lens);
+    }
+  }
+  __syncthreads();
+  // step 5: canonical codes: per-length counts, first code of each length, then rank inside the length
+  if (active && J.lens[i]) atomicAdd(&J.ctrl[3 + J.lens[i]], 1u);
+  __syncthreads();
+  if (active && i == 0) {
+    uint32_t code = 0;
+    J.ctrl[3 + 0] = 0;
+    for (int b = 1; b <= kMaxBits; b++) {
+      code = (code + J.ctrl[3 + b - 1]) << 1;
+      J.ctrl[20 + b] = code;
+    }
+  }
+  __syncthreads();
+  if (active) {
+    const int l = J.lens[i];
+    uint32_t c = 0;
+    if (l) {
+      uint32_t before = 0;
+      for (int j = 0; j < i; j++) before += (J.lens[j] == l) ? 1u : 0u;
+      c = bit_reverse(J.ctrl[20 + l] + before, l);
+    }
+    J.codes[i] = (uint16_t)c;
+  }
+  __syncthreads();
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // the kernel
 // ---------------------------------------------------------------------------------------------------------
 
@@ -380,8 +596,18 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
   uint32_t *tokens = P.tok_scratch + (size_t)blockIdx.x * kTokSlotWords;
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
+  long long t_last = 0;
+#define LZ_PROF(k)                                                    \
+  do {                                                                \
+    if (P.prof && tid == 0) {                                         \
+      const long long now_ = clock64();                               \
+      atomicAdd(&P.prof[k], (unsigned long long)(now_ - t_last));     \
+      t_last = now_;                                                  \
+    }                                                                 \
+  } while (0)
   for (;;) {
     __syncthreads();  // previous chunk fully done with shared memory
+    if (P.prof && tid == 0) t_last = clock64();
     if (tid == 0) s_misc[kMTicket] = atomicAdd(P.ticket, 1u);
     __syncthreads();
     const uint32_t c = s_misc[kMTicket];
@@ -404,8 +630,8 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
     // dictionary positions hash over the first bytes of the chunk). kMaxDist is a multiple of 16.
     load_ring(s_data, P, cs, -(((-lo_rp) + 15) & ~15), kTile + kLook);
     __syncthreads();
-    insert_positions(s_data, s_prev, s_head, lo_rp, 0);  // ends with a barrier (or is a no-op)
-    __syncthreads();
+    insert_positions(s_data, s_prev, s_head, lo_rp, 0, lo_rp);
+    LZ_PROF(kProfLoad);
 
     const int ntiles = (chunk_len + kTile - 1) / kTile;
     for (int t = 0; t < ntiles; t++) {
@@ -415,14 +641,18 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
         load_ring(s_data, P, cs, tile_rp + kLook, tile_rp + kTile + kLook);
         __syncthreads();
       }
-      insert_positions(s_data, s_prev, s_head, tile_rp, tile_rp + tile_len);
+      LZ_PROF(kProfLoad);
+      insert_positions(s_data, s_prev, s_head, tile_rp, tile_rp + tile_len, lo_rp);
+      LZ_PROF(kProfInsert);
       search_tile(s_data, s_prev, s_mlen, s_mdist, tile_rp, chunk_len, lo_rp);
       __syncthreads();
+      LZ_PROF(kProfSearch);
       if (warp == 0) {
         const int nxt = parse_tile_warp0(s_mlen, s_bitmap, (int)s_misc[kMStart], tile_len);
         if (lane == 0) s_misc[kMStart] = (uint32_t)nxt;
       }
       __syncthreads();
+      LZ_PROF(kProfParse);
       // emit tokens: rank of every start position, then token words + histograms
       {
         const int t0 = (int)tid * kRun;
@@ -454,6 +684,7 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
         if (tid == 0) s_misc[kMNTok] = base + total;
         __syncthreads();
       }
+      LZ_PROF(kProfEmit);
     }
 
     // ---- Huffman tables and exact sizes ------------------------------------------------------------------
@@ -464,16 +695,19 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
     }
     __syncthreads();
     HuffScratch *hs = reinterpret_cast<HuffScratch *>(s_head);
-    if (tid == 0) {
-      int max_l = huff_build_lengths(s_lfreq, kNumLitLen, kMaxBits, s_llen, hs[0]);
-      s_misc[kMHlit] = (uint32_t)((max_l < 256 ? 256 : max_l) + 1);
-      huff_make_codes(s_llen, kNumLitLen, s_lcode);
-    } else if (tid == 32) {
-      int max_d = huff_build_lengths(s_dfreq, kNumDist, kMaxBits, s_dlen, hs[1]);
-      s_misc[kMHdist] = (uint32_t)(max_d + 1);
-      huff_make_codes(s_dlen, kNumDist, s_dcode);
+    {
+      uint32_t *ctrl = reinterpret_cast<uint32_t *>(hs + 2) + 128;  // behind `comb` (512 bytes) in the head area
+      HuffJob jl{s_lfreq, s_llen, s_lcode, &hs[0], ctrl, kNumLitLen, 0};
+      HuffJob jd{s_dfreq, s_dlen, s_dcode, &hs[1], ctrl + 40, kNumDist, 288};
+      huff_jobs_build(jl, jd);
+      if (tid == 0) {
+        const uint32_t max_l = ctrl[2], max_d = ctrl[40 + 2];
+        s_misc[kMHlit] = (max_l < 256 ? 256 : max_l) + 1;
+        s_misc[kMHdist] = max_d + 1;
+      }
+      __syncthreads();
     }
-    __syncthreads();
+    LZ_PROF(kProfHuff);
     // body sizes: sum freq * len (+ extra bits) for the dynamic and the fixed code
     {
       uint32_t dyn = 0, fix = 0;
@@ -570,6 +804,7 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
       if (c == P.nchunks - 1) *P.total_out = need;
     }
     __syncthreads();
+    LZ_PROF(kProfSizes);
     const uint32_t mode = s_misc[kMMode];
     const uint32_t chunk_bytes = s_misc[kMChunkBytes];
     const uint64_t out_off = (uint64_t)s_misc[kMOutLo] | ((uint64_t)s_misc[kMOutHi] << 32);
@@ -720,7 +955,10 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
       dst[chunk_bytes] = 0x03;  // BFINAL=1, BTYPE=01, end-of-block
       dst[chunk_bytes + 1] = 0x00;
     }
+    __syncthreads();
+    LZ_PROF(kProfPack);
   }
+#undef LZ_PROF
 }
 
 }  // namespace dsg

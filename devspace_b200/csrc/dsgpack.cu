@@ -7,6 +7,7 @@
 #include <cuda_runtime.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -76,7 +77,7 @@ struct dsg_ctx {
   // crc
   DevBuf crc_raw;
   // deflate
-  DevBuf lz_scratch, chunk_sizes, chunk_offs;
+  DevBuf lz_scratch, chunk_sizes, chunk_offs, lz_prof;
   // pipelined path: two slots each for the arena slice, the tar segment and the compressed segment
   DevBuf slot_arena[2], slot_tar[2], slot_out[2], seg_ranges;
   Timer tim[kTimCount];
@@ -322,7 +323,11 @@ int lz_launch(dsg_ctx *ctx, cudaStream_t stream, const uint8_t *d_in, uint64_t l
   const uint64_t nchunks64 = (len + kChunk - 1) / kChunk;
   if (nchunks64 > 0xfffffff0ull) return fail(ctx, DSG_E_ARG, "input too large for one call");
   const uint32_t nchunks = (uint32_t)nchunks64;
-  const uint32_t grid = std::min<uint32_t>(nchunks, (uint32_t)ctx->sm_count);
+  uint32_t grid = std::min<uint32_t>(nchunks, (uint32_t)ctx->sm_count);
+  if (const char *g = getenv("DSG_LZ_GRID")) {  // debugging aid: fewer CTAs => more chunks per CTA
+    const long v = strtol(g, nullptr, 10);
+    if (v > 0 && (uint32_t)v < grid) grid = (uint32_t)v;
+  }
   // scratch: look-back words (one per chunk) + ticket word, token slots (one per resident CTA)
   CU(ctx->chunk_sizes.ensure(sizeof(unsigned long long) * (size_t)nchunks + 64));
   CU(ctx->lz_scratch.ensure(sizeof(uint32_t) * (size_t)kTokSlotWords * ctx->sm_count));
@@ -342,8 +347,26 @@ int lz_launch(dsg_ctx *ctx, cudaStream_t stream, const uint8_t *d_in, uint64_t l
   P.tok_scratch = ctx->lz_scratch.as<uint32_t>();
   P.total_out = d_total;
   P.write_terminator = write_terminator;
+  P.prof = nullptr;
+  static const bool prof_on = getenv("DSG_LZ_PROF") != nullptr;  // development aid: per-phase cycle counts on stderr
+  if (prof_on) {
+    CU(ctx->lz_prof.ensure(sizeof(unsigned long long) * kProfCount));
+    CU(cudaMemsetAsync(ctx->lz_prof.p, 0, sizeof(unsigned long long) * kProfCount, stream));
+    P.prof = ctx->lz_prof.as<unsigned long long>();
+  }
   lz_deflate_kernel<<<grid, kLzThreads, LzLayout::total, stream>>>(P);
   LAUNCH_CHECK();
+  if (prof_on) {
+    unsigned long long h[kProfCount];
+    CU(cudaMemcpyAsync(h, P.prof, sizeof h, cudaMemcpyDeviceToHost, stream));
+    CU(cudaStreamSynchronize(stream));
+    static const char *names[kProfCount] = {"load", "insert", "search", "parse", "emit", "huffman", "sizes", "pack"};
+    unsigned long long tot = 0;
+    for (int i = 0; i < kProfCount; i++) tot += h[i];
+    fprintf(stderr, "[lz prof] chunks=%u grid=%u cycles/chunk:", nchunks, grid);
+    for (int i = 0; i < kProfCount; i++) fprintf(stderr, " %s=%llu", names[i], h[i] / nchunks);
+    fprintf(stderr, " total=%llu\n", tot / nchunks);
+  }
   return DSG_OK;
 }
 
@@ -457,7 +480,7 @@ void dsg_ctx_destroy(dsg_ctx *ctx) {
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   for (DevBuf *b : {&ctx->crc_tab, &ctx->crc_shift, &ctx->ent_blocks, &ctx->cta_sums, &ctx->ent_off, &ctx->scalars,
                     &ctx->d_entries, &ctx->d_strtab, &ctx->d_arena, &ctx->d_tar, &ctx->d_out, &ctx->crc_raw,
-                    &ctx->lz_scratch, &ctx->chunk_sizes, &ctx->chunk_offs, &ctx->seg_ranges, &ctx->slot_arena[0],
+                    &ctx->lz_scratch, &ctx->chunk_sizes, &ctx->chunk_offs, &ctx->lz_prof, &ctx->seg_ranges, &ctx->slot_arena[0],
                     &ctx->slot_arena[1], &ctx->slot_tar[0], &ctx->slot_tar[1], &ctx->slot_out[0], &ctx->slot_out[1]})
     b->release();
   for (auto &t : ctx->tim) {

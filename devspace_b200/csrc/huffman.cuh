@@ -77,6 +77,85 @@ struct HuffScratch {
   uint16_t bl_count[kMaxBits + 2];
 };
 
+// Two-queue Huffman merge over m >= 2 leaves whose weights S.weight[0..m) are sorted ascending. Internal nodes
+// m..2m-2 are created in non-decreasing weight; S.parent[] receives the tree; returns the root index.
+// The heads of both queues are kept in registers so that an iteration costs one or two shared-memory loads.
+DSG_HD int huff_merge_sorted(HuffScratch &S, int m) {
+  const uint32_t kInf = 0xffffffffu;
+  int li = 0, ii = m, next = m;
+  uint32_t wl = S.weight[0], wi = kInf;
+  for (int k = 0; k < m - 1; k++) {
+    int a, b;
+    uint32_t wa, wb;
+    if (wl <= wi) {  // ties prefer the leaf, as zlib's heap does for equal frequency / lower depth
+      a = li++;
+      wa = wl;
+      wl = li < m ? S.weight[li] : kInf;
+    } else {
+      a = ii++;
+      wa = wi;
+      wi = ii < next ? S.weight[ii] : kInf;
+    }
+    if (wl <= wi) {
+      b = li++;
+      wb = wl;
+      wl = li < m ? S.weight[li] : kInf;
+    } else {
+      b = ii++;
+      wb = wi;
+      wi = ii < next ? S.weight[ii] : kInf;
+    }
+    const uint32_t w = wa + wb;
+    S.weight[next] = w;
+    S.parent[a] = (uint16_t)next;
+    S.parent[b] = (uint16_t)next;
+    if (ii == next) wi = w;  // the internal queue was empty: the new node is its head
+    next++;
+  }
+  return next - 1;
+}
+
+// Code lengths from the tree in S.parent[] (leaves 0..m-1 in ascending weight order = S.order[]), limited to
+// max_bits the way zlib's gen_bitlen does it: depths are propagated top-down, a node deeper than max_bits is
+// clamped and counted as an overflow (internal nodes included), then leaves are moved down level by level
+// until the Kraft sum is exactly one again, and the longest codes go to the least frequent symbols.
+DSG_HD void huff_lengths_from_tree(HuffScratch &S, int m, int root, int max_bits, uint8_t *lens) {
+  int overflow = 0;
+  S.weight[root] = 0;  // weight[] is reused as depth
+  for (int i = root - 1; i >= m; i--) {
+    int d = (int)S.weight[S.parent[i]] + 1;
+    if (d > max_bits) {
+      d = max_bits;
+      overflow++;
+    }
+    S.weight[i] = (uint32_t)d;
+  }
+  for (int b = 0; b <= max_bits + 1; b++) S.bl_count[b] = 0;
+  for (int i = 0; i < m; i++) {
+    int d = (int)S.weight[S.parent[i]] + 1;
+    if (d > max_bits) {
+      d = max_bits;
+      overflow++;
+    }
+    S.weight[i] = (uint32_t)d;
+    S.bl_count[d]++;
+  }
+  if (overflow > 0) {
+    do {
+      int bits = max_bits - 1;
+      while (S.bl_count[bits] == 0) bits--;
+      S.bl_count[bits]--;
+      S.bl_count[bits + 1] += 2;
+      S.bl_count[max_bits]--;
+      overflow -= 2;
+    } while (overflow > 0);
+    int i = 0;
+    for (int bits = max_bits; bits >= 1; bits--)
+      for (int c = S.bl_count[bits]; c > 0; c--) S.weight[i++] = (uint32_t)bits;
+  }
+  for (int i = 0; i < m; i++) lens[S.order[i]] = (uint8_t)S.weight[i];
+}
+
 // Code lengths (0 = unused symbol) for n symbols with the given frequencies, limited to max_bits.
 // At least two codes get a non-zero length so that decoders never see an incomplete one-symbol tree
 // (same convention as zlib's build_tree). Returns the highest used symbol index, or -1 when none.
@@ -113,50 +192,9 @@ DSG_HD int huff_build_lengths(const uint32_t *freq, int n, int max_bits, uint8_t
     }
     S.order[j + 1] = s;
   }
-  // two-queue Huffman: leaves 0..m-1 (sorted), internal nodes m..2m-2 are created in non-decreasing weight
   for (int i = 0; i < m; i++) S.weight[i] = freq[S.order[i]];
-  int leaf = 0, inode = m, next = m;
-  for (int k = 0; k < m - 1; k++) {
-    int a, b;
-    if (leaf < m && (inode >= next || S.weight[leaf] <= S.weight[inode])) a = leaf++; else a = inode++;
-    if (leaf < m && (inode >= next || S.weight[leaf] <= S.weight[inode])) b = leaf++; else b = inode++;
-    S.weight[next] = S.weight[a] + S.weight[b];
-    S.parent[a] = (uint16_t)next;
-    S.parent[b] = (uint16_t)next;
-    next++;
-  }
-  const int root = next - 1;
-  // depths: internal nodes were created bottom-up, so walk them top-down; reuse weight[] as depth
-  S.weight[root] = 0;
-  for (int i = root - 1; i >= m; i--) S.weight[i] = S.weight[S.parent[i]] + 1;
-  for (int b = 0; b <= max_bits + 1; b++) S.bl_count[b] = 0;
-  int overflow = 0;
-  for (int i = 0; i < m; i++) {
-    int d = (int)S.weight[S.parent[i]] + 1;
-    if (d > max_bits) {
-      d = max_bits;
-      overflow++;
-    }
-    S.weight[i] = (uint32_t)d;
-    S.bl_count[d]++;
-  }
-  if (overflow > 0) {
-    // zlib gen_bitlen repair: move one leaf down from the deepest non-full level, making room for two
-    // overflowed leaves at max_bits
-    do {
-      int bits = max_bits - 1;
-      while (S.bl_count[bits] == 0) bits--;
-      S.bl_count[bits]--;
-      S.bl_count[bits + 1] += 2;
-      S.bl_count[max_bits]--;
-      overflow -= 2;
-    } while (overflow > 0);
-    // reassign: the least frequent symbols get the longest codes
-    int i = 0;
-    for (int bits = max_bits; bits >= 1; bits--)
-      for (int c = S.bl_count[bits]; c > 0; c--) S.weight[i++] = (uint32_t)bits;
-  }
-  for (int i = 0; i < m; i++) lens[S.order[i]] = (uint8_t)S.weight[i];
+  const int root = huff_merge_sorted(S, m);
+  huff_lengths_from_tree(S, m, root, max_bits, lens);
   return max_sym;
 }
 

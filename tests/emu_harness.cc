@@ -88,6 +88,7 @@ int emu_lz_deflate(const uint8_t *in, uint64_t len, const uint8_t *dict, uint32_
   P.total_out = &total;
   P.error = &error;
   P.write_terminator = 1;
+
   emu::launch(dim3(grid), dim3(kLzThreads), LzLayout::total, [&] { lz_deflate_kernel(P); });
   *out_len = total;
   return error ? DSG_E_CAPACITY : 0;

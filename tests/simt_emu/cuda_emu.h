@@ -50,6 +50,8 @@ struct Fiber {
   ucontext_t ctx;
   char *stack = nullptr;
   bool done = false;
+  bool at_barrier = false;   // parked in __syncthreads: not scheduled until the barrier generation changes
+  unsigned bar_gen_seen = 0;
   dim3 tid;
 };
 
@@ -123,6 +125,7 @@ inline void launch(dim3 grid, dim3 block, size_t dyn_bytes, const std::function<
         for (unsigned t = 0; t < nthreads; t++) {
           Fiber &f = fibers[t];
           f.done = false;
+          f.at_barrier = false;
           f.tid = dim3(t % block.x, (t / block.x) % block.y, t / (block.x * block.y));
           getcontext(&f.ctx);
           f.ctx.uc_stack.ss_sp = f.stack;
@@ -132,14 +135,40 @@ inline void launch(dim3 grid, dim3 block, size_t dyn_bytes, const std::function<
         }
         blockIdx = dim3(bx, by, bz);
         unsigned long spins = 0;
+        // EMU_SCHED=reverse|random runs the fibers in another order: code that silently relies on threads
+        // executing in thread-id order (e.g. atomics "arriving" in stream order) then fails here too
+        static const char *sched_env = getenv("EMU_SCHED");
+        std::vector<unsigned> order(nthreads);
+        for (unsigned t = 0; t < nthreads; t++) order[t] = t;
+        if (sched_env && sched_env[0] == 'r' && sched_env[1] == 'e') std::reverse(order.begin(), order.end());
+        unsigned lcg = 12345u + bx;
         while (bs.live > 0) {
-          for (unsigned t = 0; t < nthreads; t++) {
-            if (fibers[t].done) continue;
+          unsigned ran = 0;
+          if (sched_env && sched_env[0] == 'r' && sched_env[1] == 'a')
+            for (unsigned t = nthreads - 1; t > 0; t--) {
+              lcg = lcg * 1664525u + 1013904223u;
+              std::swap(order[t], order[(lcg >> 8) % (t + 1)]);
+            }
+          for (unsigned oi = 0; oi < nthreads; oi++) {
+            const unsigned t = order[oi];
+            Fiber &f = fibers[t];
+            if (f.done) continue;
+            if (f.at_barrier && f.bar_gen_seen == bs.bar_gen) continue;  // still parked
             bs.current = (int)t;
-            threadIdx = fibers[t].tid;
-            swapcontext(&bs.sched, &fibers[t].ctx);
+            threadIdx = f.tid;
+            swapcontext(&bs.sched, &f.ctx);
+            ran++;
           }
-          if (++spins > 50000000ul) throw std::runtime_error("emu: deadlock (barrier never satisfied)");
+          if (ran == 0) {
+            // everybody alive is parked at the barrier: threads that exited do not take part
+            if (bs.bar_arrived >= bs.live && bs.live > 0) {
+              bs.bar_arrived = 0;
+              bs.bar_gen++;
+            } else {
+              throw std::runtime_error("emu: deadlock (barrier never satisfied)");
+            }
+          }
+          if (++spins > 2000000000ul) throw std::runtime_error("emu: livelock");
         }
         cur_block() = nullptr;
       }
@@ -181,21 +210,23 @@ inline uint64_t warp_collective(unsigned mask, uint64_t v, F combine) {
 // ---- synchronisation -------------------------------------------------------------------------------
 inline void __syncthreads() {
   emu::BlockState *b = emu::cur_block();
+  emu::Fiber &f = b->fibers[b->current];
   const unsigned my_gen = b->bar_gen;
   b->bar_arrived++;
-  while (true) {
-    if (b->bar_gen != my_gen) return;
-    if (b->bar_arrived >= b->live) {  // exited threads do not take part
-      b->bar_arrived = 0;
-      b->bar_gen++;
-      return;
-    }
-    emu::yield();
+  if (b->bar_arrived >= b->live) {  // last arriver releases everybody (exited threads do not take part)
+    b->bar_arrived = 0;
+    b->bar_gen++;
+    return;
   }
+  f.at_barrier = true;
+  f.bar_gen_seen = my_gen;
+  while (b->bar_gen == my_gen) emu::yield();  // parked: the scheduler skips this fiber until the release
+  f.at_barrier = false;
 }
 inline void __syncwarp(unsigned mask = 0xffffffffu) {
   emu::warp_collective(mask, 0, [](const uint64_t *, unsigned, unsigned) { return (uint64_t)0; });
 }
+inline long long clock64() { return 0; }
 inline void __threadfence() {}
 inline void __threadfence_block() {}
 

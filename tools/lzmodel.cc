@@ -31,7 +31,7 @@ struct Tok {
   uint16_t dist; // or literal byte
 };
 
-static uint64_t g_steps = 0, g_searches = 0, g_cmpbytes = 0;
+static uint64_t g_steps = 0, g_searches = 0, g_cmpbytes = 0, g_work = 0, g_fut = 0;
 
 static size_t zlib6(const uint8_t *d, size_t n) {
   z_stream zs;
@@ -67,7 +67,7 @@ int main(int argc, char **argv) {
   if (fread(d.data(), 1, n, f) != n) return 2;
   fclose(f);
 
-  std::vector<int32_t> head(1 << HB), prev(n + 1);
+  std::vector<int32_t> head(1 << HB), prev(n + 1), start_of(n + 1, -1);
   std::vector<uint16_t> mlen(CHUNK), mdist(CHUNK);
   std::vector<Tok> toks;
   uint64_t total_bits = 0, n_stored = 0, n_fixed = 0, n_dyn = 0, n_tok = 0, n_match = 0, hdr_bits = 0;
@@ -76,20 +76,48 @@ int main(int argc, char **argv) {
     size_t ce = cs + CHUNK < n ? cs + CHUNK : n;
     size_t ds = cs > (size_t)WIN ? cs - WIN : 0;
     std::fill(head.begin(), head.end(), -1);
-    for (size_t p = ds; p < ce; p++) {
-      if (p + 4 > n) { prev[p] = -1; continue; }
-      uint32_t h = hash4(&d[p]);
-      prev[p] = head[h];
-      head[h] = (int32_t)p;
+    {
+      static int SCR = getenv("SCRAMBLE") ? atoi(getenv("SCRAMBLE")) : 0;
+      std::vector<size_t> ord;
+      for (size_t p = ds; p < ce; p++) ord.push_back(p);
+      if (SCR > 1) {
+        // rounds of SCR consecutive positions (aligned to the chunk start like the kernel's tiles), random order inside
+        size_t i0 = 0;
+        while (i0 < ord.size()) {
+          size_t i1 = i0 + SCR - ((ord[i0] - ds) % SCR);
+          if (i1 > ord.size()) i1 = ord.size();
+          for (size_t k = i1 - 1; k > i0; k--) { size_t j = i0 + rand() % (k - i0 + 1); std::swap(ord[k], ord[j]); }
+          i0 = i1;
+        }
+      }
+      static int SNAP = getenv("SNAP") ? atoi(getenv("SNAP")) : 0;
+      size_t k0 = 0;
+      for (size_t k = 0; k < ord.size(); k++) {
+        size_t p = ord[k];
+        static int RUNX = getenv("RUNX") ? atoi(getenv("RUNX")) : 0;
+        if (p + 4 > n) { prev[p] = -1; }
+        else {
+          uint32_t h = hash4(&d[p]);
+          prev[p] = head[h];
+          bool interior = RUNX && p > ds && memcmp(&d[p], &d[p - 1], 4) == 0;
+          if (!interior) head[h] = (int32_t)p;
+        }
+        // end of a round: snapshot the head for every position of the round
+        bool round_end = (k + 1 == ord.size()) || (SCR > 1 && ((k + 1 + (ord.size() ? 0 : 0)) , ((ord[k0] - ds) / SCR != (ord[k + 1] - ds) / SCR)));
+        if (SNAP && round_end) {
+          for (size_t j = k0; j <= k; j++) { size_t pp = ord[j]; start_of[pp] = (pp + 4 > n) ? -1 : head[hash4(&d[pp])]; }
+          k0 = k + 1;
+        }
+      }
     }
     // per-position best match
     std::vector<uint8_t> deep(CHUNK, 0);
-    int inh_len = 0, inh_dist = 0;
+    int inh_len = 0, inh_dist = 0, rep_dist = 0;
     size_t cover_end = cs;   // policy 3: end of the match the thread-local speculative parse is inside of
     size_t lazy_pos = (size_t)-1;
     int lazy_len = 0;
     for (size_t p = cs; p < ce; p++) {
-      if ((p - cs) % RUN == 0) { inh_len = 0; cover_end = p; lazy_pos = (size_t)-1; }
+      if ((p - cs) % RUN == 0) { inh_len = 0; cover_end = p; lazy_pos = (size_t)-1; rep_dist = 0; }
       int maxlen = (int)(ce - p < 258 ? ce - p : 258);
       int best = 0, bdist = 0;
       // inherited candidate from p-1
@@ -99,7 +127,7 @@ int main(int argc, char **argv) {
         if (best >= NICE) depth = 0;
         else if (best >= 32 && POLICY >= 2) depth = 0;
         else if (best >= GOOD) depth = DEPTH / 4;
-      } else if (POLICY == 4) {
+      } else if (POLICY == 4 || POLICY == 5) {
         depth = INSIDE;
         if (best >= NICE) depth = 0;
       } else if (POLICY == 3) {
@@ -108,10 +136,34 @@ int main(int argc, char **argv) {
         else depth = DEPTH;                                                 // token start: full effort
         if (best >= NICE) depth = 0;
       }
+      static int REP = getenv("REP") ? atoi(getenv("REP")) : 0;
+      static int RUNX2 = getenv("RUNX") ? atoi(getenv("RUNX")) : 0;
+      if (RUNX2 && maxlen >= MINM && best < NICE && p > ds && memcmp(&d[p], &d[p - 1], 4) == 0) {
+        const uint8_t *a = &d[p], *b = &d[p - 1];
+        int l = 0;
+        while (l < maxlen && a[l] == b[l]) l++;
+        if (l > best || (l == best && 1 < bdist)) { best = l; bdist = 1; }
+        if (best >= GOOD && depth > DEPTH / 4) depth = DEPTH / 4;
+        if (best >= NICE) depth = 0;
+      }
+      if (REP && maxlen >= MINM && best < NICE) {   // explicit near probes: distance 1 and the run's last distance
+        int cand[2] = {1, rep_dist};
+        for (int ci = 0; ci < 2; ci++) {
+          int dd = cand[ci];
+          if (dd <= 0 || (size_t)dd > p - ds) continue;
+          const uint8_t *a = &d[p], *b = &d[p - dd];
+          int l = 0;
+          while (l < maxlen && a[l] == b[l]) l++;
+          if (l >= MINM && (l > best || (l == best && dd < bdist))) { best = l; bdist = dd; }
+        }
+      }
       if (maxlen >= MINM && depth > 0) {
         g_searches++;
-        int32_t q = prev[p];
+        static int SNAP2 = getenv("SNAP") ? atoi(getenv("SNAP")) : 0;
+        int32_t q = SNAP2 ? start_of[p] : prev[p];
+        static int FF = getenv("FUTURE_FREE") ? atoi(getenv("FUTURE_FREE")) : 0;
         while (q >= 0 && depth-- > 0) {
+          if ((size_t)q >= p) { if (FF) depth++; g_steps++; g_fut++; q = prev[q]; continue; }   // same-round entry later in the stream
           size_t dist = p - q;
           if (dist > (size_t)MAXDIST) break;
           g_steps++;
@@ -120,7 +172,7 @@ int main(int argc, char **argv) {
             int l = 0;
             while (l < maxlen && a[l] == b[l]) l++;
             g_cmpbytes += l;
-            if (l > best && l >= MINM) {
+            if (l >= MINM && (l > best || (l == best && (int)dist < bdist))) {
               best = l;
               bdist = (int)dist;
               if (l >= NICE || l >= maxlen) break;
@@ -144,6 +196,43 @@ int main(int argc, char **argv) {
       }
       inh_len = best;
       inh_dist = bdist;
+      if (best >= MINM) rep_dist = bdist;
+    }
+    if (POLICY == 5) {
+      // refine without a first parse: deep-search every position that is not a pure inheritor of its predecessor
+      std::vector<size_t> work;
+      for (size_t p = cs; p < ce; p++) {
+        bool inh = p > cs && (p - cs) % RUN != 0 && mlen[p - cs] >= (LAZY > 100 ? MINM : LAZY) && mlen[p - 1 - cs] == mlen[p - cs] + 1 &&
+                   mdist[p - 1 - cs] == mdist[p - cs];
+        if (!inh) work.push_back(p);
+      }
+      g_work += work.size();
+      std::vector<uint16_t> nl(mlen), nd(mdist);
+      for (size_t p : work) {
+        int maxlen = (int)(ce - p < 258 ? ce - p : 258);
+        int best = mlen[p - cs], bdist = mdist[p - cs];
+        int depth = DEPTH;
+        if (p > cs && mlen[p - 1 - cs] >= GOOD) depth = DEPTH / 4;
+        if (best >= NICE || maxlen < MINM) continue;
+        g_searches++;
+        int32_t c = prev[p];
+        while (c >= 0 && depth-- > 0) {
+          size_t dist = p - c;
+          if (dist > (size_t)MAXDIST) break;
+          g_steps++;
+          const uint8_t *a = &d[p], *b = &d[c];
+          if (best < MINM || (a[best] == b[best] && a[best - 1] == b[best - 1])) {
+            int l = 0;
+            while (l < maxlen && a[l] == b[l]) l++;
+            g_cmpbytes += l;
+            if (l > best && l >= MINM) { best = l; bdist = (int)dist; if (l >= NICE || l >= maxlen) break; }
+          }
+          c = prev[c];
+        }
+        nl[p - cs] = (uint16_t)best;
+        nd[p - cs] = (uint16_t)bdist;
+      }
+      mlen = nl; mdist = nd;
     }
     if (POLICY == 4) {
       // two-phase refine: the loop above ran with the shallow depth (INSIDE); now parse, deep-search the token
@@ -195,7 +284,7 @@ int main(int argc, char **argv) {
     while (p < ce) {
       int l = mlen[p - cs];
       bool take = l >= MINM;
-      if (take && (POLICY == 4 || l < LAZY) && p + 1 < ce && mlen[p + 1 - cs] > l) take = false;
+      if (take && (POLICY >= 4 || l < LAZY) && p + 1 < ce && mlen[p + 1 - cs] > l) take = false;
       if (take) {
         toks.push_back({(uint16_t)l, mdist[p - cs]});
         uint32_t lc = len_code(l), dc = dist_code(mdist[p - cs]);
@@ -244,9 +333,9 @@ int main(int argc, char **argv) {
   size_t ours = (total_bits + 7) / 8 + 2;
   size_t z = zlib6(d.data(), n);
   printf("%s n=%zu ours=%zu zlib6=%zu ratio=%.4f | chunks stored/fixed/dyn=%llu/%llu/%llu tokens=%llu matches=%llu "
-         "hdr=%.2f%% | searches/pos=%.3f steps/pos=%.2f cmpbytes/pos=%.2f\n",
+         "hdr=%.2f%% | searches/pos=%.3f steps/pos=%.2f cmpbytes/pos=%.2f deepfrac=%.3f\n",
          argv[1], n, ours, z, (double)ours / z, (unsigned long long)n_stored, (unsigned long long)n_fixed,
          (unsigned long long)n_dyn, (unsigned long long)n_tok, (unsigned long long)n_match,
-         100.0 * hdr_bits / 8 / ours, (double)g_searches / n, (double)g_steps / n, (double)g_cmpbytes / n);
+         100.0 * hdr_bits / 8 / ours, (double)g_searches / n, (double)g_steps / n, (double)g_cmpbytes / n, (double)g_work / n); printf("future skips/pos=%.2f\n", (double)g_fut / n);
   return 0;
 }
