@@ -25,9 +25,12 @@
 //               resident) + shared-memory histograms
 //   per chunk   Huffman code lengths (two-queue merge, zlib-style overflow repair), code-length RLE, exact
 //               sizes of the three encodings -> chunk size known BEFORE any bit is written
-//               decoupled look-back over the previous chunks' sizes -> output offset (no gather pass)
 //               bit packing: per-token bit lengths -> block scan -> atomicOr into a shared-memory window ->
-//               realigned 128-bit stores to the final position
+//               128-bit stores into the chunk's slot of a scratch buffer (stored chunks write nothing)
+// followed by lz_scan_kernel (exclusive prefix of the chunk sizes) and lz_gather_kernel (slots -> final byte
+// offsets, stored chunks straight from the input). A first version placed the output with a decoupled
+// look-back inside the main kernel; CTAs then spent 20 % of their time waiting for slower predecessors
+// (profiles/r01_lz_phases.md), and the wait chain serialises completely once a CTA owns a run of chunks.
 // Roofline: the kernel is bound by shared-memory bandwidth / LSU issue (random 1-2 byte reads), not by HBM:
 // algorithmic HBM bytes per chunk are 64 KiB read (+32 KiB dictionary re-read from L2) + C written.
 #pragma once
@@ -50,7 +53,7 @@ constexpr int kHashBits = 13;
 constexpr int kHashSize = 1 << kHashBits;
 constexpr int kMinMatch = 4;
 constexpr int kMaxMatch = 258;
-constexpr int kDepth = 48;
+constexpr int kDepth = 32;
 constexpr int kNice = 128;
 constexpr int kGood = 8;
 constexpr int kRun = kTile / kLzThreads;  // 16 consecutive positions per thread
@@ -61,6 +64,7 @@ constexpr int kBatchTokens = 2048;        // tokens per bit-packing batch (<= 48
 constexpr int kTokPerThread = kBatchTokens / kLzThreads;
 constexpr uint32_t kTokMatch = 0x80000000u;
 constexpr int kTokSlotWords = kChunk + 64;  // per-CTA token scratch (u32), worst case all literals + EOB
+constexpr int kSlotBytes = kChunk + 128;    // per-chunk output slot in the scratch buffer (16-byte aligned)
 
 // Upper bound of the raw deflate output for n input bytes: a chunk never exceeds its stored encoding
 // (two stored blocks for a 64 KiB chunk), plus the 2-byte terminator.
@@ -70,11 +74,11 @@ DSG_HD uint64_t lz_deflate_bound(uint64_t n) { return n + 10 * ((n + kChunk - 1)
 struct LzLayout {
   static constexpr int data = 0;                                  // kRing + kLook + 48 bytes (mirror + slack)
   static constexpr int prev = data + kRing + kLook + 48;          // u16[kRing]
-  static constexpr int head = prev + 2 * kRing;                   // u32[kHashSize]; Huffman scratch afterwards
+  static constexpr int head = prev + 2 * kRing;                   // u32[kHashSize]
   static constexpr int mlen = head + 4 * kHashSize;               // u8[kTile]      } reused as the bit-packing
   static constexpr int mdist = mlen + kTile;                      // u16[kTile]     } window after the last tile
   static constexpr int bitmap = mdist + 2 * kTile;                // u32[kTile/32] token-start flags
-  static constexpr int lfreq = bitmap + kTile / 8;                // u32[288]
+  static constexpr int lfreq = bitmap + kTile / 8 + 128;          // u32[288] (32 parse exits sit behind the bitmap)
   static constexpr int dfreq = lfreq + 4 * 288;                   // u32[32]
   static constexpr int llen = dfreq + 4 * 32;                     // u8[288] literal/length code lengths
   static constexpr int dlen = llen + 288;                         // u8[32]
@@ -84,11 +88,12 @@ struct LzLayout {
   static constexpr int clcode = cllen + 32;                       // u16[32]
   static constexpr int rle = clcode + 2 * 32;                     // u16[320]
   static constexpr int misc = rle + 2 * 320;                      // u32[64] scalars / scan scratch
-  static constexpr int total = misc + 4 * 64 + 16;
+  static constexpr int huff = misc + 4 * 64 + 16;                 // 2 x HuffScratch + comb[512] + ctrl[80]
+  static constexpr int total = huff + 2 * 4064 + 512 + 4 * 80 + 16;
 };
+static_assert(sizeof(HuffScratch) <= 4064, "HuffScratch grew");
 static_assert(LzLayout::prev % 16 == 0 && LzLayout::head % 16 == 0 && LzLayout::mlen % 16 == 0, "alignment");
 static_assert(kTile + 2 * kTile >= kStageBytes, "bit-packing window must fit in the match arrays");
-static_assert(sizeof(HuffScratch) * 2 + 512 + 4 * 80 <= 4 * kHashSize, "Huffman scratch must fit in the head table");
 static_assert(LzLayout::total <= 227 * 1024, "shared memory budget");
 static_assert(kMaxDist % 16 == 0 && kLook % 16 == 0, "ring loads move 16-byte granules");
 
@@ -102,25 +107,19 @@ struct LzParams {
   uint64_t len;               // bytes
   const uint8_t *dict;        // up to 32 KiB that precede `in` in the member (previous segment), or null
   uint32_t dict_len;
-  uint8_t *out;               // output base
-  uint64_t out_cap;
+  uint8_t *slots;             // per-chunk output slots, kSlotBytes apart (scratch)
+  uint32_t *chunk_meta;       // per chunk: (bytes << 1) | stored flag (scratch)
   uint32_t nchunks;
+  uint32_t run_chunks;        // consecutive chunks one ticket hands out (the LZ window slides across them)
   uint32_t *ticket;           // zeroed before launch
-  unsigned long long *state;  // per chunk look-back word: (bytes << 2) | flag; zeroed before launch
   uint32_t *tok_scratch;      // gridDim.x * kTokSlotWords
-  uint64_t *total_out;        // deflate bytes produced by this launch (written by the last chunk's CTA)
-  uint32_t *error;            // set to 1 when out_cap is too small
-  int write_terminator;       // append the final empty fixed block (03 00)
   unsigned long long *prof;   // optional: cycles per phase, summed over CTAs (thread 0's clock64 deltas)
 };
 
 enum { kProfLoad = 0, kProfInsert, kProfSearch, kProfParse, kProfEmit, kProfHuff, kProfSizes, kProfPack, kProfCount };
 
-DSG_D uint32_t ring_slot(int rp /* chunk-relative position, >= -kDict */) {
-  uint32_t x = (uint32_t)(rp + kDict);
-  if (x >= 2u * kRing) x -= 2u * kRing;
-  else if (x >= (uint32_t)kRing) x -= kRing;
-  return x;
+DSG_D uint32_t ring_slot(int rp /* run-relative position, >= -kDict */) {
+  return (uint32_t)(rp + kDict) % (uint32_t)kRing;
 }
 
 DSG_D uint32_t hash4(uint32_t v) { return (v * 2654435761u) >> (32 - kHashBits); }
@@ -212,162 +211,199 @@ DSG_D void load_ring(uint8_t *s_data, const LzParams &P, int64_t cs, int rp0, in
   }
 }
 
-// Inserts positions [rp0, rp1) into the hash chains in EXACT stream order (nearest candidate first), 512
-// positions per round, one per thread. Inside a round the threads race, so a thread does a lock-free sorted
-// insertion: it walks past entries of its own round that lie LATER in the stream (at most a handful, they can
-// only be ahead by < 512 positions) and links itself below them with a compare-and-swap on the link it came
-// through (32-bit CAS on the head table, 16-bit CAS on a prev[] entry). Exact order matters: chains that are
-// only ordered per round cost 1-3 % of compressed size (tools/lzmodel.cc, SCRAMBLE=512).
+// Inserts positions [rp0, rp1) into the hash chains in EXACT stream order (nearest candidate first), 1024
+// positions per round, two per thread. Inside a round the threads race, so a thread does a lock-free sorted
+// insertion: it walks past entries of its own round that lie LATER in the stream (they can only be ahead by
+// < 1024 positions) and links itself below them with a compare-and-swap on the link it came through (32-bit
+// CAS on the head table, 16-bit CAS on a prev[] entry). Exact order matters: chains that are only ordered per
+// round cost 1-3 % of compressed size (tools/lzmodel.cc, SCRAMBLE=512).
 // Positions in the interior of a byte run (the five bytes p-1..p+3 are equal) are not inserted: every one of
 // them would land in the same bucket (quadratic walks, useless candidates); the search gives them the
-// distance-1 candidate directly. They still get a chain start (prev[] = head after the round).
-DSG_D void insert_positions(const uint8_t *s_data, uint16_t *s_prev, uint32_t *s_head, int rp0, int rp1, int lo_rp) {
-  unsigned short *prev16 = reinterpret_cast<unsigned short *>(s_prev);
-  for (int base = rp0; base < rp1; base += kLzThreads) {
-    const int rp = base + (int)threadIdx.x;
-    const bool on = rp < rp1;
-    uint32_t slot = 0, h = 0;
-    bool interior = false;
-    if (on) {
-      slot = ring_slot(rp);
-      const uint32_t v = load4(s_data + slot);
-      h = hash4(v);
-      interior = rp > lo_rp && v == load4(s_data + ring_slot(rp - 1));
-      if (!interior) {
-        bool at_head = true;
-        uint32_t holder = h;  // the link we would be written into: head[h], or prev[holder]
-        int walked = 0;
-        for (;;) {
-          const uint32_t nxt = at_head ? s_head[holder] : (uint32_t)prev16[holder];
-          if (nxt != kNil && ++walked < 2 * kLzThreads) {  // the bound only guards against stale links
-            int fwd = (int)nxt - (int)slot;
-            if (fwd < 0) fwd += kRing;
-            if (fwd > 0 && fwd < kLzThreads) {  // an entry of this round that is later in the stream
-              at_head = false;
-              holder = nxt;
-              continue;
-            }
-          }
-          prev16[slot] = (unsigned short)nxt;
-          __threadfence_block();  // our own link is visible before we become reachable
-          const uint32_t seen = at_head ? atomicCAS(&s_head[holder], nxt, slot)
-                                        : (uint32_t)atomicCAS(&prev16[holder], (unsigned short)nxt, (unsigned short)slot);
-          if (seen == nxt) break;  // else somebody linked in first: look at the same link again
-        }
+// distance-1 candidate directly. Their chain start is whatever the head holds when they look (an entry of the
+// same round that lies ahead of them is skipped by the search).
+constexpr int kInsRound = 2 * kLzThreads;
+
+DSG_D void insert_one(const uint8_t *s_data, unsigned short *prev16, uint32_t *s_head, int rp, int lo_rp) {
+  const uint32_t slot = ring_slot(rp);
+  const uint32_t v = load4(s_data + slot);
+  const uint32_t h = hash4(v);
+  if (rp > lo_rp && v == load4(s_data + ring_slot(rp - 1))) {  // interior of a byte run
+    prev16[slot] = (unsigned short)s_head[h];
+    return;
+  }
+  bool at_head = true;
+  uint32_t holder = h;  // the link we would be written into: head[h], or prev[holder]
+  int walked = 0;
+  for (;;) {
+    const uint32_t nxt = at_head ? s_head[holder] : (uint32_t)prev16[holder];
+    if (nxt != kNil && ++walked < 2 * kInsRound) {  // the bound only guards against stale links
+      int fwd = (int)nxt - (int)slot;
+      if (fwd < 0) fwd += kRing;
+      if (fwd > 0 && fwd < kInsRound) {  // an entry of this round that is later in the stream
+        at_head = false;
+        holder = nxt;
+        continue;
       }
     }
-    __syncthreads();
-    if (on && interior) prev16[slot] = (unsigned short)s_head[h];
-    __syncthreads();  // the next round must not move the heads under the readers above
+    // Our own link is written before we become reachable: both are shared-memory operations of this thread
+    // and the shared-memory pipeline of an SM performs a warp's accesses in program order.
+    prev16[slot] = (unsigned short)nxt;
+#if defined(DSG_EMU)
+    __threadfence_block();
+#else
+    asm volatile("" ::: "memory");
+#endif
+    const uint32_t seen = at_head ? atomicCAS(&s_head[holder], nxt, slot)
+                                  : (uint32_t)atomicCAS(&prev16[holder], (unsigned short)nxt, (unsigned short)slot);
+    if (seen == nxt) break;  // else somebody linked in first: look at the same link again
   }
 }
 
-// Longest match for every position of the tile. tile_rp = chunk-relative position of the tile start,
-// chunk_len = bytes in this chunk, lo_rp = lowest chunk-relative position holding real data (-dictionary).
-// One thread owns a run of kRun consecutive positions; a position inherits (len-1, dist) from its
-// predecessor. The loop is flattened: every iteration performs ONE chain step (or finishes a position and
-// sets up the next), so the lanes of a warp do not wait for the lane with the longest chain at each position.
-DSG_D void search_tile(const uint8_t *s_data, const uint16_t *s_prev, uint8_t *s_mlen, uint16_t *s_mdist, int tile_rp,
-                       int chunk_len, int lo_rp) {
-  const int t0 = (int)threadIdx.x * kRun;
-  int inh_len = 0, inh_dist = 0;
-  int j = 0;
-  bool setup = true;
-  int tp = 0, maxlen = 0, best = 0, bdist = 0, depth = 0, max_back = 0, last_d = 0;
-  uint32_t slot = 0, q = kNil, aw = 0, v_prev = 0;
-  int skips = 0;
-  const uint8_t *a = s_data;
-  while (j < kRun) {
-    if (setup) {
-      setup = false;
-      tp = t0 + j;
-      const int rp = tile_rp + tp;
-      maxlen = chunk_len - rp < kMaxMatch ? chunk_len - rp : kMaxMatch;
-      best = 0;
-      bdist = 0;
-      depth = 0;
-      q = kNil;
-      last_d = 0;
-      if (maxlen >= kMinMatch) {
-        if (inh_len > kMinMatch) {
-          best = inh_len - 1 < maxlen ? inh_len - 1 : maxlen;
-          bdist = inh_dist;
-        }
-        slot = ring_slot(rp);
-        a = s_data + slot;
-        max_back = rp - lo_rp < kMaxDist ? rp - lo_rp : kMaxDist;
-        const uint32_t v = load4(a);
-        if (j == 0) v_prev = max_back > 0 ? load4(s_data + ring_slot(rp - 1)) : ~v;
-        if (v == v_prev && max_back > 0 && best < kNice) {
-          // interior of a byte run: the distance-1 candidate (never in the chains, see insert_positions)
-          const uint8_t *b1 = s_data + ring_slot(rp - 1);
-          int l = 4;
-          while (l < maxlen) {
-            const uint32_t x = load4(a + l) ^ load4(b1 + l);
-            if (x) {
-              l += (__ffs((int)x) - 1) >> 3;
-              break;
-            }
-            l += 4;
-          }
-          if (l > maxlen) l = maxlen;
-          if (l > best || (l == best && bdist > 1)) {
-            best = l;
-            bdist = 1;
-          }
-        }
-        v_prev = v;
-        depth = best >= kNice ? 0 : (best >= kGood ? kDepth / 4 : kDepth);
-        q = s_prev[slot];
-        skips = 0;
-        aw = load4(a + (best >= 3 ? best - 3 : 0));  // the four bytes a better match has to reproduce last
+DSG_D void insert_positions(const uint8_t *s_data, uint16_t *s_prev, uint32_t *s_head, int rp0, int rp1, int lo_rp) {
+  unsigned short *prev16 = reinterpret_cast<unsigned short *>(s_prev);
+  for (int base = rp0; base < rp1; base += kInsRound) {
+    const int r0 = base + (int)threadIdx.x, r1 = r0 + kLzThreads;
+    if (r0 < rp1) insert_one(s_data, prev16, s_head, r0, lo_rp);
+    if (r1 < rp1) insert_one(s_data, prev16, s_head, r1, lo_rp);
+    __syncthreads();  // rounds are ordered
+  }
+}
+
+// Longest match for every position of the tile. tile_rp = run-relative position of the tile start, chunk_end =
+// run-relative end of the chunk (matches never cross it), lo_rp = lowest position holding real data.
+// A thread owns kRun consecutive positions, split into kWays independent sub-runs that it advances in an
+// interleaved fashion (two dependent shared-memory chains in flight per thread: the walk is latency bound, ncu
+// shows 16 warps cannot hide it, profiles/r01_lz_ncu.md). Inside a sub-run a position inherits (len-1, dist)
+// from its predecessor. Each sub-run is a small state machine -- an iteration performs ONE chain step, ONE
+// 4-byte compare step, or finishes a position and sets up the next -- so the lanes of a warp never wait for
+// the lane with the longest chain or the longest compare.
+constexpr int kWays = 1;
+constexpr int kSubRun = kRun / kWays;
+
+struct SearchWay {
+  int j, st, pos0;  // position index inside the sub-run, state, tile-relative first position
+  int inh_len, inh_dist;
+  int maxlen, best, bdist, depth, max_back, last_d, skips;
+  int cl, cd;  // compare state: bytes matched so far, distance of the candidate
+  uint32_t slot, q, qn, aw, v_prev;
+  const uint8_t *a, *cb;
+};
+
+DSG_D void search_way_init(SearchWay &w, const uint8_t *s_data, int tile_rp, int pos0, int lo_rp) {
+  w.j = 0;
+  w.st = 0;
+  w.pos0 = pos0;
+  w.inh_len = w.inh_dist = 0;
+  w.maxlen = w.best = w.bdist = w.depth = w.max_back = w.last_d = w.skips = w.cl = w.cd = 0;
+  w.slot = ring_slot(tile_rp + pos0);
+  w.q = w.qn = kNil;
+  w.aw = 0;
+  w.a = s_data + w.slot;
+  w.cb = s_data;
+  if (tile_rp + pos0 > lo_rp) w.v_prev = load4(s_data + ring_slot(tile_rp + pos0 - 1));
+  else w.v_prev = ~load4(w.a);
+}
+
+DSG_D void search_way_step(SearchWay &w, const uint8_t *s_data, const uint16_t *s_prev, uint8_t *s_mlen,
+                           uint16_t *s_mdist, int tile_rp, int chunk_end, int lo_rp) {
+  enum { kSetup = 0, kWalk = 1, kCmp = 2 };
+  if (w.st == kSetup) {
+    const int rp = tile_rp + w.pos0 + w.j;
+    w.maxlen = chunk_end - rp < kMaxMatch ? chunk_end - rp : kMaxMatch;
+    w.best = 0;
+    w.bdist = 0;
+    w.depth = 0;
+    w.q = kNil;
+    w.last_d = 0;
+    w.skips = 0;
+    w.st = kWalk;
+    const uint32_t v = load4(w.a);
+    if (w.maxlen >= kMinMatch) {
+      if (w.inh_len > kMinMatch) {
+        w.best = w.inh_len - 1 < w.maxlen ? w.inh_len - 1 : w.maxlen;
+        w.bdist = w.inh_dist;
+      }
+      w.max_back = rp - lo_rp < kMaxDist ? rp - lo_rp : kMaxDist;
+      w.depth = w.best >= kNice ? 0 : (w.best >= kGood ? kDepth / 4 : kDepth);
+      w.q = s_prev[w.slot];
+      w.aw = load4(w.a + (w.best >= 3 ? w.best - 3 : 0));  // the four bytes a better match has to reproduce last
+      if (v == w.v_prev && w.max_back > 0 && w.best < kNice && !(w.bdist == 1 && w.best >= kMinMatch)) {
+        // interior of a byte run: try the distance-1 candidate (never in the chains, see insert_one)
+        w.cb = w.a - 1 + (w.slot == 0 ? kRing : 0);
+        w.cd = 1;
+        w.cl = 4;  // v == v_prev: the first four bytes are known to match
+        w.qn = w.q;
+        w.st = kCmp;
       }
     }
-    if (depth > 0 && q != kNil) {
-      depth--;
-      int d = (int)slot - (int)q;
+    w.v_prev = v;
+  } else if (w.st == kWalk) {
+    if (w.depth > 0 && w.q != kNil) {
+      w.depth--;
+      int d = (int)w.slot - (int)w.q;
       if (d <= 0) d += kRing;
-      if (d > kRing - kLzThreads && skips < 64) {
-        // chain start of a run-interior position may be an entry of the same round that is later in the stream
-        skips++;
-        depth++;
-        q = s_prev[q];
-      } else if (d > max_back || d <= last_d) {
-        q = kNil;  // left the window, or a stale link (chains are in exact stream order: distances grow)
+      if (d > kRing - kInsRound && w.skips < 64) {
+        // the chain start of a run-interior position may be an entry of its own round that lies ahead
+        w.skips++;
+        w.depth++;
+        w.q = s_prev[w.q];
+      } else if (d > w.max_back || d <= w.last_d) {
+        w.q = kNil;  // left the window, or a stale link (chains are in exact stream order: distances grow)
       } else {
-        last_d = d;
-        const uint8_t *b = s_data + q;
-        const uint32_t qn = s_prev[q];  // next link, fetched before the compare so that its latency overlaps
-        if (load4(b + (best >= 3 ? best - 3 : 0)) == aw) {
-          int l = 0;
-          while (l < maxlen) {
-            const uint32_t x = load4(a + l) ^ load4(b + l);
-            if (x) {
-              l += (__ffs((int)x) - 1) >> 3;
-              break;
-            }
-            l += 4;
-          }
-          if (l > maxlen) l = maxlen;
-          if (l >= kMinMatch && l > best) {
-            best = l;
-            bdist = d;
-            if (l >= kNice || l >= maxlen) depth = 0;
-            else aw = load4(a + best - 3);
-          }
+        w.last_d = d;
+        const uint8_t *b = s_data + w.q;
+        w.qn = s_prev[w.q];  // next link, fetched before the compare so that its latency overlaps
+        if (load4(b + (w.best >= 3 ? w.best - 3 : 0)) == w.aw) {
+          w.cb = b;
+          w.cd = d;
+          w.cl = 0;
+          w.st = kCmp;
+        } else {
+          w.q = w.qn;
         }
-        q = qn;
       }
     } else {
-      if (best < kMinMatch) best = 0;
-      s_mlen[tp] = (uint8_t)(best ? best - 3 : 0);  // 0 = no match, else len-3 in 1..255
-      s_mdist[tp] = (uint16_t)bdist;
-      inh_len = best;
-      inh_dist = bdist;
-      j++;
-      setup = true;
+      if (w.best < kMinMatch) w.best = 0;
+      s_mlen[w.pos0 + w.j] = (uint8_t)(w.best ? w.best - 3 : 0);  // 0 = no match, else len-3 in 1..255
+      s_mdist[w.pos0 + w.j] = (uint16_t)w.bdist;
+      w.inh_len = w.best;
+      w.inh_dist = w.bdist;
+      w.j++;
+      w.slot++;
+      w.a++;
+      if (w.slot == (uint32_t)kRing) {
+        w.slot = 0;
+        w.a = s_data;
+      }
+      w.st = kSetup;
+    }
+  } else {  // kCmp: one 4-byte step of the candidate at distance cd
+    const uint32_t x = w.cl < w.maxlen ? (load4(w.a + w.cl) ^ load4(w.cb + w.cl)) : 1u;
+    if (x == 0) {
+      w.cl += 4;
+    } else {
+      int l = w.cl < w.maxlen ? w.cl + ((__ffs((int)x) - 1) >> 3) : w.maxlen;
+      if (l > w.maxlen) l = w.maxlen;
+      if (l >= kMinMatch && (l > w.best || (l == w.best && w.cd < w.bdist))) {
+        w.best = l;
+        w.bdist = w.cd;
+        if (l >= kNice || l >= w.maxlen) w.depth = 0;
+        else w.aw = load4(w.a + w.best - 3);
+      }
+      w.q = w.qn;
+      w.st = kWalk;
     }
   }
+}
+
+DSG_D void search_tile(const uint8_t *s_data, const uint16_t *s_prev, uint8_t *s_mlen, uint16_t *s_mdist, int tile_rp,
+                       int chunk_end, int lo_rp) {
+  const int t0 = (int)threadIdx.x * kRun;
+  // (two interleaved sub-runs per thread were measured slower than one: the kernel is bound by instruction
+  // issue at ~10 active lanes per warp, not by the latency of a single chain, profiles/r01_lz_phases.md)
+  SearchWay w0;
+  search_way_init(w0, s_data, tile_rp, t0, lo_rp);
+  while (w0.j < kSubRun) search_way_step(w0, s_data, s_prev, s_mlen, s_mdist, tile_rp, chunk_end, lo_rp);
 }
 
 // next(p) for the stateless lazy parse; tp is tile-relative, tile_len = positions of this tile inside the chunk
@@ -422,42 +458,42 @@ DSG_D int parse_tile_warp0(const uint8_t *s_mlen, uint32_t *s_bitmap, int start,
     if (cur) bm[widx] = cur;
   }
   const int exit_p = p;  // first token start at or beyond the end of the sub-range
+  // serial fix-up by lane 0 over the 32 sub-ranges (exits travel through shared memory: no shuffle / warp
+  // barrier per sub-range): a sub-range whose true entry equals its speculated entry keeps its marks.
+  uint32_t *s_exit = s_bitmap + kTile / 32;  // 32 words behind the bitmap
+  s_exit[lane] = (uint32_t)exit_p;
   __syncwarp();
-  // serial fix-up: lane l learns where lane l-1 really ended
-  int true_in = exit_p;  // lane 0's exit is final
-  for (int l = 1; l < 32; l++) {
-    const int prev_exit = __shfl_sync(0xffffffffu, true_in, l - 1);
-    if (lane == l) {
-      if (sub_lo >= tile_len) {
-        true_in = prev_exit;  // nothing here; pass through
-      } else if (prev_exit >= sub_hi) {
-        clear_bits(bm, sub_lo, sub_hi);  // the whole sub-range lies inside an earlier match
-        true_in = prev_exit;
-      } else if (prev_exit == sub_lo) {
-        true_in = exit_p;  // speculation was right
+  int result = 0;
+  if (lane == 0) {
+    int true_in = (int)s_exit[0];  // sub-range 0 was parsed from the true start
+    for (int l = 1; l < 32; l++) {
+      const int lo = l * kSub;
+      if (lo >= tile_len) break;  // nothing beyond the tile
+      const int hi = (lo + kSub < tile_len) ? lo + kSub : tile_len;
+      if (true_in == lo) {
+        true_in = (int)s_exit[l];  // speculation was right
+      } else if (true_in >= hi) {
+        clear_bits(bm, lo, hi);  // the whole sub-range lies inside an earlier match
       } else {
-        clear_bits(bm, sub_lo, prev_exit);
-        int q = prev_exit;
-        int out = exit_p;
+        clear_bits(bm, lo, true_in);
+        int q = true_in;
         bool converged = false;
-        while (q < sub_hi) {
+        while (q < hi) {
           if (bm[q >> 5] & (1u << (q & 31))) {
             converged = true;
             break;
           }
           bm[q >> 5] |= 1u << (q & 31);
           const int nq = q + parse_step(s_mlen, q, tile_len);
-          clear_bits(bm, q + 1, nq < sub_hi ? nq : sub_hi);
+          clear_bits(bm, q + 1, nq < hi ? nq : hi);
           q = nq;
         }
-        if (!converged) out = q;
-        true_in = out;
+        true_in = converged ? (int)s_exit[l] : q;
       }
     }
-    __syncwarp();
+    result = true_in - tile_len;  // >= 0: first token start of the following tile, relative to it
   }
-  const int last_exit = __shfl_sync(0xffffffffu, true_in, 31);
-  return last_exit - tile_len;  // >= 0
+  return __shfl_sync(0xffffffffu, result, 0);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -605,46 +641,55 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
       t_last = now_;                                                  \
     }                                                                 \
   } while (0)
+  const uint32_t R = P.run_chunks;
+  const uint32_t nruns = (P.nchunks + R - 1) / R;
   for (;;) {
-    __syncthreads();  // previous chunk fully done with shared memory
+    __syncthreads();  // previous run fully done with shared memory
     if (P.prof && tid == 0) t_last = clock64();
     if (tid == 0) s_misc[kMTicket] = atomicAdd(P.ticket, 1u);
     __syncthreads();
-    const uint32_t c = s_misc[kMTicket];
-    if (c >= P.nchunks) break;
-    const int64_t cs = (int64_t)c * kChunk;
-    const int chunk_len = (int)((int64_t)P.len - cs < kChunk ? (int64_t)P.len - cs : kChunk);
-    // dictionary actually available before this chunk; positions farther back than kMaxDist are never
-    // referenced (their ring slots are reused by the first tile's look-ahead)
-    const int64_t avail = cs + (P.dict ? (int64_t)P.dict_len : 0);
+    const uint32_t run = s_misc[kMTicket];
+    if (run >= nruns) break;
+    // A run is a stretch of R consecutive chunks compressed by this CTA with ONE sliding LZ window: the hash
+    // chains and the ring carry over from chunk to chunk, only the first chunk has to hash its dictionary.
+    const int64_t rs = (int64_t)run * R * kChunk;  // stream offset of the run
+    const int64_t avail = rs + (P.dict ? (int64_t)P.dict_len : 0);
     const int lo_rp = -(int)(avail < (int64_t)kMaxDist ? avail : (int64_t)kMaxDist);
-
-    for (uint32_t i = tid; i < 288; i += kLzThreads) s_lfreq[i] = 0;
-    if (tid < 32) s_dfreq[tid] = 0;
     for (uint32_t i = tid; i < (uint32_t)kHashSize; i += kLzThreads) s_head[i] = kNil;
-    if (tid == 0) {
-      s_misc[kMStart] = 0;
-      s_misc[kMNTok] = 0;
-    }
     // dictionary + first tile + look-ahead are resident before the dictionary is hashed (the last three
-    // dictionary positions hash over the first bytes of the chunk). kMaxDist is a multiple of 16.
-    load_ring(s_data, P, cs, -(((-lo_rp) + 15) & ~15), kTile + kLook);
+    // dictionary positions hash over the first bytes of the run). kMaxDist is a multiple of 16.
+    load_ring(s_data, P, rs, -(((-lo_rp) + 15) & ~15), kTile + kLook);
     __syncthreads();
     insert_positions(s_data, s_prev, s_head, lo_rp, 0, lo_rp);
     LZ_PROF(kProfLoad);
 
+    for (uint32_t k = 0; k < R; k++) {
+    const uint32_t c = run * R + k;
+    if (c >= P.nchunks) break;
+    const int64_t cs = (int64_t)c * kChunk;
+    const int crp = (int)(k * kChunk);  // run-relative position of the chunk start
+    const int chunk_len = (int)((int64_t)P.len - cs < kChunk ? (int64_t)P.len - cs : kChunk);
+    __syncthreads();
+    for (uint32_t i = tid; i < 288; i += kLzThreads) s_lfreq[i] = 0;
+    if (tid < 32) s_dfreq[tid] = 0;
+    if (tid == 0) {
+      s_misc[kMStart] = 0;
+      s_misc[kMNTok] = 0;
+    }
+    __syncthreads();
+
     const int ntiles = (chunk_len + kTile - 1) / kTile;
     for (int t = 0; t < ntiles; t++) {
-      const int tile_rp = t * kTile;
-      const int tile_len = chunk_len - tile_rp < kTile ? chunk_len - tile_rp : kTile;
-      if (t > 0) {  // next tile's bytes + look-ahead replace the oldest dictionary bytes
-        load_ring(s_data, P, cs, tile_rp + kLook, tile_rp + kTile + kLook);
+      const int tile_rp = crp + t * kTile;
+      const int tile_len = chunk_len - t * kTile < kTile ? chunk_len - t * kTile : kTile;
+      if (tile_rp > 0) {  // next tile's bytes + look-ahead replace the oldest dictionary bytes
+        load_ring(s_data, P, rs, tile_rp + kLook, tile_rp + kTile + kLook);
         __syncthreads();
       }
       LZ_PROF(kProfLoad);
       insert_positions(s_data, s_prev, s_head, tile_rp, tile_rp + tile_len, lo_rp);
       LZ_PROF(kProfInsert);
-      search_tile(s_data, s_prev, s_mlen, s_mdist, tile_rp, chunk_len, lo_rp);
+      search_tile(s_data, s_prev, s_mlen, s_mdist, tile_rp, crp + chunk_len, lo_rp);
       __syncthreads();
       LZ_PROF(kProfSearch);
       if (warp == 0) {
@@ -694,7 +739,7 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
       s_lfreq[kEob] += 1;
     }
     __syncthreads();
-    HuffScratch *hs = reinterpret_cast<HuffScratch *>(s_head);
+    HuffScratch *hs = reinterpret_cast<HuffScratch *>(smem + LzLayout::huff);  // two scratches, 4064 bytes apart
     {
       uint32_t *ctrl = reinterpret_cast<uint32_t *>(hs + 2) + 128;  // behind `comb` (512 bytes) in the head area
       HuffJob jl{s_lfreq, s_llen, s_lcode, &hs[0], ctrl, kNumLitLen, 0};
@@ -775,59 +820,16 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
       s_misc[kMHdrBits] = hbits;
       s_misc[kMHclen] = (uint32_t)hclen;
       s_misc[kMNRle] = (uint32_t)nr;
-      // decoupled look-back: exclusive prefix of the previous chunks' sizes
-      unsigned long long excl = 0;
-      if (c > 0) {
-        atomicExch(&P.state[c], ((unsigned long long)bytes << 2) | 1ull);
-        int64_t i = (int64_t)c - 1;
-        for (;;) {
-          unsigned long long v;
-          do {
-            v = atomicAdd(&P.state[i], 0ull);
-          } while ((v & 3ull) == 0ull);
-          excl += v >> 2;
-          if ((v & 3ull) == 2ull) break;
-          i--;
-        }
-      }
-      __threadfence();
-      atomicExch(&P.state[c], ((excl + bytes) << 2) | 2ull);
-      s_misc[kMOutLo] = (uint32_t)excl;
-      s_misc[kMOutHi] = (uint32_t)(excl >> 32);
-      uint32_t err = 0;
-      const uint64_t need = excl + bytes + ((c == P.nchunks - 1 && P.write_terminator) ? 2 : 0);
-      if (need > P.out_cap) {
-        err = 1;
-        atomicExch(P.error, 1u);
-      }
-      s_misc[kMError] = err;
-      if (c == P.nchunks - 1) *P.total_out = need;
+      P.chunk_meta[c] = (bytes << 1) | (mode == 0 ? 1u : 0u);
     }
     __syncthreads();
     LZ_PROF(kProfSizes);
     const uint32_t mode = s_misc[kMMode];
     const uint32_t chunk_bytes = s_misc[kMChunkBytes];
-    const uint64_t out_off = (uint64_t)s_misc[kMOutLo] | ((uint64_t)s_misc[kMOutHi] << 32);
-    if (s_misc[kMError]) continue;
-    uint8_t *dst = P.out + out_off;
+    uint8_t *dst = P.slots + (size_t)c * kSlotBytes;
 
     if (mode == 0) {
-      // stored: one or two blocks, bytes straight from the input
-      const uint8_t *src = P.in + cs;
-      uint32_t done = 0, o = 0;
-      while (done < (uint32_t)chunk_len) {
-        const uint32_t n = (uint32_t)chunk_len - done < kStoredMax ? (uint32_t)chunk_len - done : kStoredMax;
-        if (tid == 0) {
-          dst[o + 0] = 0;
-          dst[o + 1] = (uint8_t)(n & 0xff);
-          dst[o + 2] = (uint8_t)(n >> 8);
-          dst[o + 3] = (uint8_t)(~n & 0xff);
-          dst[o + 4] = (uint8_t)((~n >> 8) & 0xff);
-        }
-        block_copy_unaligned(dst + o + 5, src + done, n, tid, kLzThreads);
-        done += n;
-        o += n + 5;
-      }
+      // stored: the gather kernel copies the bytes straight from the input
     } else {
       // ---- bit packing ----------------------------------------------------------------------------------
       const uint32_t ntok = s_misc[kMNTok];
@@ -951,14 +953,92 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
         }
       }
     }
-    if (c == P.nchunks - 1 && P.write_terminator && tid == 0) {
-      dst[chunk_bytes] = 0x03;  // BFINAL=1, BTYPE=01, end-of-block
-      dst[chunk_bytes + 1] = 0x00;
-    }
     __syncthreads();
     LZ_PROF(kProfPack);
+    }  // chunks of the run
   }
 #undef LZ_PROF
+}
+
+// Exclusive prefix of the chunk sizes (single CTA): offs[c] = byte offset of chunk c in the output,
+// *total_out = all chunks (+2 for the terminator); *error = 1 when the output buffer is too small.
+__global__ void __launch_bounds__(1024) lz_scan_kernel(const uint32_t *__restrict__ chunk_meta, uint32_t nchunks,
+                                                        uint64_t *__restrict__ offs, uint64_t out_cap,
+                                                        int write_terminator, uint64_t *__restrict__ total_out,
+                                                        uint32_t *__restrict__ error) {
+  __shared__ uint64_t warp_tot[32];
+  __shared__ uint64_t carry_s;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (uint32_t base = 0; base < nchunks; base += 1024) {
+    const uint32_t i = base + threadIdx.x;
+    const uint64_t v = i < nchunks ? (uint64_t)(chunk_meta[i] >> 1) : 0;
+    uint64_t x = v;
+    for (int o = 1; o < 32; o <<= 1) {
+      uint64_t y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= (uint32_t)o) x += y;
+    }
+    if (lane == 31) warp_tot[warp] = x;
+    __syncthreads();
+    if (warp == 0) {
+      const uint64_t t = warp_tot[lane];
+      uint64_t sc = t;
+      for (int o = 1; o < 32; o <<= 1) {
+        uint64_t y = __shfl_up_sync(0xffffffffu, sc, o);
+        if (lane >= (uint32_t)o) sc += y;
+      }
+      warp_tot[lane] = sc - t;
+    }
+    __syncthreads();
+    const uint64_t excl = carry_s + warp_tot[warp] + (x - v);
+    if (i < nchunks) offs[i] = excl;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry_s = excl + v;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const uint64_t tot = carry_s + (write_terminator ? 2 : 0);
+    *total_out = tot;
+    if (tot > out_cap) atomicExch(error, 1u);
+  }
+}
+
+// One CTA per chunk: moves the chunk's bytes from its slot (or, for stored chunks, from the input behind
+// 5-byte stored-block headers) to its final offset. The last chunk appends the terminator.
+__global__ void __launch_bounds__(256)
+lz_gather_kernel(const uint8_t *__restrict__ in, uint64_t len, const uint8_t *__restrict__ slots,
+                 const uint32_t *__restrict__ chunk_meta, const uint64_t *__restrict__ offs, uint32_t nchunks,
+                 uint8_t *__restrict__ out, int write_terminator, const uint32_t *__restrict__ error) {
+  if (*error) return;  // output too small: nothing is written
+  const uint32_t c = blockIdx.x;
+  const uint32_t meta = chunk_meta[c];
+  const uint32_t bytes = meta >> 1;
+  uint8_t *dst = out + offs[c];
+  if (meta & 1u) {
+    const uint64_t cs = (uint64_t)c * kChunk;
+    const uint32_t chunk_len = (uint32_t)(len - cs < (uint64_t)kChunk ? len - cs : (uint64_t)kChunk);
+    uint32_t done = 0, o = 0;
+    while (done < chunk_len) {
+      const uint32_t n = chunk_len - done < kStoredMax ? chunk_len - done : kStoredMax;
+      if (threadIdx.x == 0) {
+        dst[o + 0] = 0;  // BFINAL=0, BTYPE=00
+        dst[o + 1] = (uint8_t)(n & 0xff);
+        dst[o + 2] = (uint8_t)(n >> 8);
+        dst[o + 3] = (uint8_t)(~n & 0xff);
+        dst[o + 4] = (uint8_t)((~n >> 8) & 0xff);
+      }
+      block_copy_unaligned(dst + o + 5, in + cs + done, n, threadIdx.x, 256);
+      done += n;
+      o += n + 5;
+    }
+  } else {
+    block_copy_unaligned(dst, slots + (size_t)c * kSlotBytes, bytes, threadIdx.x, 256);
+  }
+  if (write_terminator && c == nchunks - 1 && threadIdx.x == 0) {
+    dst[bytes] = 0x03;  // BFINAL=1, BTYPE=01, end-of-block
+    dst[bytes + 1] = 0x00;
+  }
 }
 
 }  // namespace dsg

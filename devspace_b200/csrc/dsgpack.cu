@@ -77,7 +77,7 @@ struct dsg_ctx {
   // crc
   DevBuf crc_raw;
   // deflate
-  DevBuf lz_scratch, chunk_sizes, chunk_offs, lz_prof;
+  DevBuf lz_scratch, chunk_sizes, chunk_slots, chunk_offs, lz_prof;
   // pipelined path: two slots each for the arena slice, the tar segment and the compressed segment
   DevBuf slot_arena[2], slot_tar[2], slot_out[2], seg_ranges;
   Timer tim[kTimCount];
@@ -323,30 +323,38 @@ int lz_launch(dsg_ctx *ctx, cudaStream_t stream, const uint8_t *d_in, uint64_t l
   const uint64_t nchunks64 = (len + kChunk - 1) / kChunk;
   if (nchunks64 > 0xfffffff0ull) return fail(ctx, DSG_E_ARG, "input too large for one call");
   const uint32_t nchunks = (uint32_t)nchunks64;
-  uint32_t grid = std::min<uint32_t>(nchunks, (uint32_t)ctx->sm_count);
+  // chunks per run: long runs amortise hashing the dictionary, short ones keep every SM busy on small inputs
+  uint32_t run_chunks = std::max<uint32_t>(1, std::min<uint32_t>(8, nchunks / (4 * (uint32_t)ctx->sm_count)));
+  if (const char *g = getenv("DSG_LZ_RUN")) {
+    const long v = strtol(g, nullptr, 10);
+    if (v > 0 && v <= 64) run_chunks = (uint32_t)v;
+  }
+  const uint32_t nruns = (nchunks + run_chunks - 1) / run_chunks;
+  uint32_t grid = std::min<uint32_t>(nruns, (uint32_t)ctx->sm_count);
   if (const char *g = getenv("DSG_LZ_GRID")) {  // debugging aid: fewer CTAs => more chunks per CTA
     const long v = strtol(g, nullptr, 10);
     if (v > 0 && (uint32_t)v < grid) grid = (uint32_t)v;
   }
-  // scratch: look-back words (one per chunk) + ticket word, token slots (one per resident CTA)
-  CU(ctx->chunk_sizes.ensure(sizeof(unsigned long long) * (size_t)nchunks + 64));
+  // scratch: per-chunk output slots + sizes + offsets, the ticket word, token slots (one per resident CTA)
+  const size_t meta_bytes = (sizeof(uint64_t) + sizeof(uint32_t)) * (size_t)nchunks + 64;
+  CU(ctx->chunk_sizes.ensure(meta_bytes));
+  CU(ctx->chunk_slots.ensure((size_t)kSlotBytes * nchunks));
   CU(ctx->lz_scratch.ensure(sizeof(uint32_t) * (size_t)kTokSlotWords * ctx->sm_count));
-  CU(cudaMemsetAsync(ctx->chunk_sizes.p, 0, sizeof(unsigned long long) * (size_t)nchunks + 64, stream));
+  uint64_t *offs = ctx->chunk_sizes.as<uint64_t>();
+  uint32_t *meta = reinterpret_cast<uint32_t *>(offs + nchunks);
+  uint32_t *ticket = meta + nchunks;
+  CU(cudaMemsetAsync(ticket, 0, sizeof(uint32_t), stream));
   LzParams P;
   P.in = d_in;
   P.len = len;
   P.dict = dict_len ? d_dict : nullptr;
   P.dict_len = dict_len;
-  P.out = d_out;
-  P.out_cap = out_cap;
+  P.slots = ctx->chunk_slots.as<uint8_t>();
+  P.chunk_meta = meta;
   P.nchunks = nchunks;
-  unsigned long long *words = ctx->chunk_sizes.as<unsigned long long>();
-  P.state = words;
-  P.ticket = reinterpret_cast<uint32_t *>(words + nchunks);
-  P.error = d_error;
+  P.run_chunks = run_chunks;
+  P.ticket = ticket;
   P.tok_scratch = ctx->lz_scratch.as<uint32_t>();
-  P.total_out = d_total;
-  P.write_terminator = write_terminator;
   P.prof = nullptr;
   static const bool prof_on = getenv("DSG_LZ_PROF") != nullptr;  // development aid: per-phase cycle counts on stderr
   if (prof_on) {
@@ -355,6 +363,10 @@ int lz_launch(dsg_ctx *ctx, cudaStream_t stream, const uint8_t *d_in, uint64_t l
     P.prof = ctx->lz_prof.as<unsigned long long>();
   }
   lz_deflate_kernel<<<grid, kLzThreads, LzLayout::total, stream>>>(P);
+  LAUNCH_CHECK();
+  lz_scan_kernel<<<1, 1024, 0, stream>>>(meta, nchunks, offs, out_cap, write_terminator, d_total, d_error);
+  LAUNCH_CHECK();
+  lz_gather_kernel<<<nchunks, 256, 0, stream>>>(d_in, len, P.slots, meta, offs, nchunks, d_out, write_terminator, d_error);
   LAUNCH_CHECK();
   if (prof_on) {
     unsigned long long h[kProfCount];
@@ -480,7 +492,7 @@ void dsg_ctx_destroy(dsg_ctx *ctx) {
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   for (DevBuf *b : {&ctx->crc_tab, &ctx->crc_shift, &ctx->ent_blocks, &ctx->cta_sums, &ctx->ent_off, &ctx->scalars,
                     &ctx->d_entries, &ctx->d_strtab, &ctx->d_arena, &ctx->d_tar, &ctx->d_out, &ctx->crc_raw,
-                    &ctx->lz_scratch, &ctx->chunk_sizes, &ctx->chunk_offs, &ctx->lz_prof, &ctx->seg_ranges, &ctx->slot_arena[0],
+                    &ctx->lz_scratch, &ctx->chunk_sizes, &ctx->chunk_slots, &ctx->chunk_offs, &ctx->lz_prof, &ctx->seg_ranges, &ctx->slot_arena[0],
                     &ctx->slot_arena[1], &ctx->slot_tar[0], &ctx->slot_tar[1], &ctx->slot_out[0], &ctx->slot_out[1]})
     b->release();
   for (auto &t : ctx->tim) {
@@ -853,7 +865,8 @@ static int pack_host_pipelined(dsg_ctx *ctx, const dsg_entry *entries, size_t n,
   }
   if (gzip && ctx->opts.level != DSG_LEVEL_STORED) {
     const uint64_t nch = (std::min(S, T) + kChunk - 1) / kChunk;
-    CU(ctx->chunk_sizes.ensure(sizeof(unsigned long long) * (size_t)nch + 64));
+    CU(ctx->chunk_sizes.ensure((sizeof(uint64_t) + sizeof(uint32_t)) * (size_t)nch + 64));
+    CU(ctx->chunk_slots.ensure((size_t)kSlotBytes * nch));
     CU(ctx->lz_scratch.ensure(sizeof(uint32_t) * (size_t)kTokSlotWords * ctx->sm_count));
   }
   if (gzip) {

@@ -71,20 +71,32 @@ def _vocab(device, nwords: int = 6000, seed: int = 7):
 
 
 def text_like(nbytes: int, seed: int, device="cpu") -> torch.Tensor:
-    """JS/JSON-like token soup with a Zipf vocabulary and short-range repetition (gzip -6 ratio ~3.5-4.5x)."""
+    """JS/JSON-like source text (gzip -6 ratio ~3.5-4.5x): lines are drawn from a pool of line templates (token
+    sequences over a Zipf vocabulary) and re-emitted with a few tokens swapped for fresh identifiers, the way
+    real code repeats statements with different names. Most of the redundancy therefore sits in repeated
+    phrases of 20-80 bytes at distances up to tens of KiB, as in real source trees, not in the unigram
+    statistics of a token soup."""
     if nbytes <= 0:
         return torch.zeros(0, dtype=torch.uint8, device=device)
     flat, starts, lens, probs = _vocab(device)
     g = _gen(seed, device)
     mean_len = float((lens.double() * probs.double()).sum())
-    ntok = int(nbytes / mean_len * 1.15) + 64
-    ids = torch.multinomial(probs, ntok, replacement=True, generator=g)
-    # short-range repetition: with p=0.35 a token repeats the one 8..64 tokens back (identifiers recur locally)
-    rep = torch.rand(ntok, generator=g, device=device) < 0.35
-    back = torch.randint(8, 64, (ntok,), generator=g, device=device)
-    src = torch.arange(ntok, device=device) - back
-    ids = torch.where(rep & (src >= 0), ids[src.clamp(min=0)], ids)
+    TPL, LINE = 384, 12                                    # templates per stream, tokens per line
+    ntok = int(nbytes / mean_len * 1.2) + 4 * LINE
+    nlines = ntok // LINE + 1
+    tpl = torch.multinomial(probs, TPL * LINE, replacement=True, generator=g).view(TPL, LINE)
+    # template choice: mostly recent templates (locality), sometimes any
+    pick = torch.randint(0, TPL, (nlines,), generator=g, device=device)
+    near = (torch.arange(nlines, device=device) // 24 * 7 + torch.randint(0, 24, (nlines,), generator=g, device=device)) % TPL
+    pick = torch.where(torch.rand(nlines, generator=g, device=device) < 0.8, near, pick)
+    ids = tpl[pick]                                        # (nlines, LINE)
+    # substitute ~25 % of the tokens by fresh draws (identifiers / literals differ from line to line)
+    fresh = torch.multinomial(probs, nlines * LINE, replacement=True, generator=g).view(nlines, LINE)
+    sub = torch.rand(nlines, LINE, generator=g, device=device) < 0.05
+    ids = torch.where(sub, fresh, ids).reshape(-1)
+    ntok = ids.numel()
     tl = lens[ids]
+    # every line ends with a newline token's bytes already present in many templates; lengths as drawn
     ends = torch.cumsum(tl, 0)
     total = int(ends[-1])
     tok_of_byte = torch.repeat_interleave(torch.arange(ntok, device=device), tl)

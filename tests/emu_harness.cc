@@ -61,7 +61,7 @@ int emu_tar_build(const dsg_entry *entries, uint32_t n, const char *strtab, uint
 
 // Mirrors lz_deflate_run in dsgpack.cu: one launch of the persistent LZ77+Huffman kernel.
 int emu_lz_deflate(const uint8_t *in, uint64_t len, const uint8_t *dict, uint32_t dict_len, uint8_t *out,
-                   uint64_t cap, uint64_t *out_len, uint32_t grid) {
+                   uint64_t cap, uint64_t *out_len, uint32_t grid, uint32_t run_chunks) {
   if (len == 0) {
     out[0] = 3;
     out[1] = 0;
@@ -69,8 +69,12 @@ int emu_lz_deflate(const uint8_t *in, uint64_t len, const uint8_t *dict, uint32_
     return 0;
   }
   const uint32_t nchunks = (uint32_t)((len + kChunk - 1) / kChunk);
-  if (grid == 0 || grid > nchunks) grid = nchunks;
-  std::vector<unsigned long long> state(nchunks + 8, 0);
+  if (run_chunks == 0) run_chunks = 1;
+  const uint32_t nruns = (nchunks + run_chunks - 1) / run_chunks;
+  if (grid == 0 || grid > nruns) grid = nruns;
+  std::vector<uint8_t> slots((size_t)nchunks * kSlotBytes, 0xAB);
+  std::vector<uint32_t> meta(nchunks, 0);
+  std::vector<uint64_t> offs(nchunks, 0);
   std::vector<uint32_t> tok((size_t)grid * kTokSlotWords, 0xDEADBEEF);
   uint32_t ticket = 0, error = 0;
   uint64_t total = 0;
@@ -79,17 +83,18 @@ int emu_lz_deflate(const uint8_t *in, uint64_t len, const uint8_t *dict, uint32_
   P.len = len;
   P.dict = dict;
   P.dict_len = dict_len;
-  P.out = out;
-  P.out_cap = cap;
+  P.slots = slots.data();
+  P.chunk_meta = meta.data();
   P.nchunks = nchunks;
+  P.run_chunks = run_chunks;
   P.ticket = &ticket;
-  P.state = state.data();
   P.tok_scratch = tok.data();
-  P.total_out = &total;
-  P.error = &error;
-  P.write_terminator = 1;
-
+  P.prof = nullptr;
   emu::launch(dim3(grid), dim3(kLzThreads), LzLayout::total, [&] { lz_deflate_kernel(P); });
+  emu::launch(dim3(1), dim3(1024), 0, [&] { lz_scan_kernel(meta.data(), nchunks, offs.data(), cap, 1, &total, &error); });
+  emu::launch(dim3(nchunks), dim3(256), 0, [&] {
+    lz_gather_kernel(in, len, slots.data(), meta.data(), offs.data(), nchunks, out, 1, &error);
+  });
   *out_len = total;
   return error ? DSG_E_CAPACITY : 0;
 }

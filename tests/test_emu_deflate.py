@@ -21,7 +21,7 @@ def _lib():
     return lib
 
 
-def emu_deflate(data: bytes, grid: int = 0, dict_: bytes = b""):
+def emu_deflate(data: bytes, grid: int = 0, dict_: bytes = b"", run_chunks: int = 1):
     L = _lib()
     a = np.frombuffer(data, np.uint8)
     d = np.frombuffer(dict_, np.uint8)
@@ -30,7 +30,8 @@ def emu_deflate(data: bytes, grid: int = 0, dict_: bytes = b""):
     n = ctypes.c_uint64()
     rc = L.emu_lz_deflate(ctypes.c_void_p(a.ctypes.data if len(data) else None), ctypes.c_uint64(len(data)),
                           ctypes.c_void_p(d.ctypes.data if len(dict_) else None), ctypes.c_uint32(len(dict_)),
-                          ctypes.c_void_p(out.ctypes.data), ctypes.c_uint64(cap), ctypes.byref(n), ctypes.c_uint32(grid))
+                          ctypes.c_void_p(out.ctypes.data), ctypes.c_uint64(cap), ctypes.byref(n), ctypes.c_uint32(grid),
+                          ctypes.c_uint32(run_chunks))
     assert rc == 0
     return out[: n.value].tobytes()
 
@@ -77,6 +78,9 @@ def test_emulated_deflate_persistent_grid_and_dictionary():
     one = emu_deflate(data, grid=1)            # one CTA walks all four chunks through the ticket counter
     two = emu_deflate(data, grid=3)
     assert one == two                           # chunk outputs do not depend on which CTA ran them
+    slid = emu_deflate(data, run_chunks=3)      # one sliding window across three chunks, then a run of one
+    assert zlib.decompress(slid, -15) == data
+    assert abs(len(slid) - len(one)) <= 0.005 * len(one)
     assert zlib.decompress(one, -15) == data
     # a segment that continues a member: the previous 32 KiB are handed in as the dictionary
     head, tail = data[:100_000], data[100_000:]
