@@ -21,7 +21,7 @@ SYMBOLS = [
     "dsg_pinned_alloc", "dsg_pinned_free", "dsg_entry_header_bytes", "dsg_tar_size", "dsg_gzip_bound",
     "dsg_shard_bounds", "dsg_pack", "dsg_pack_tar_only", "dsg_pack_device", "dsg_get_stats", "dsg_dev_tar_build",
     "dsg_dev_crc32", "dsg_dev_deflate", "dsg_dev_gzip", "dsg_dev_alloc", "dsg_dev_free", "dsg_dev_upload",
-    "dsg_dev_download",
+    "dsg_dev_download", "dsg_crc32_noalloc",
 ]
 
 
@@ -100,5 +100,6 @@ def load(build_if_missing: bool = True):
     lib.dsg_dev_free.restype = None
     lib.dsg_dev_upload.argtypes = [vp, vp, vp, sz]
     lib.dsg_dev_download.argtypes = [vp, vp, vp, sz]
+    lib.dsg_crc32_noalloc.argtypes = [vp, sz, POINTER(c_uint32), c_char_p, sz]
     _lib = lib
     return lib

@@ -181,6 +181,17 @@ int dsg_dev_deflate(dsg_ctx *ctx, const uint8_t *d_in, size_t len, int level, ui
 int dsg_dev_gzip(dsg_ctx *ctx, const uint8_t *d_in, size_t len, int level, uint8_t *d_out, size_t out_cap,
                  size_t *out_len);
 
+/* No counterpart in the reference. CRC32-IEEE of d_buf[0,len) (device memory on the CURRENT device) for callers
+ * that cannot go to the CUDA allocator when they need the checksum: a process whose device memory was handed
+ * out completely at start-up, or a loop that cannot take cudaMalloc/cudaFree's device-wide synchronisation or an
+ * out-of-memory failure mid-upload. Needs no dsg_ctx and allocates nothing: the per-tile partial results live
+ * in a static device array inside the library (55 KB with the lookup tables, resident on every GPU that loads
+ * the library until the process exits), which limits len to 1 GiB -- longer inputs return DSG_E_CAPACITY with a
+ * message in err. The first call on a device does a one-time set-up (device current; make it before any stream
+ * capture). All calls on a device share the array: do not let two calls overlap on the GPU. Runs on the default
+ * stream and returns once *crc (host memory) holds the result. err/err_len: optional buffer for error text. */
+int dsg_crc32_noalloc(const uint8_t *d_buf, size_t len, uint32_t *crc, char *err, size_t err_len);
+
 /* Plain device memory helpers so that ctypes / cgo callers need no CUDA binding of their own. */
 void *dsg_dev_alloc(dsg_ctx *ctx, size_t bytes);
 void dsg_dev_free(dsg_ctx *ctx, void *d_ptr);
