@@ -92,7 +92,7 @@ def text_like(nbytes: int, seed: int, device="cpu") -> torch.Tensor:
     ids = tpl[pick]                                        # (nlines, LINE)
     # substitute ~25 % of the tokens by fresh draws (identifiers / literals differ from line to line)
     fresh = torch.multinomial(probs, nlines * LINE, replacement=True, generator=g).view(nlines, LINE)
-    sub = torch.rand(nlines, LINE, generator=g, device=device) < 0.05
+    sub = torch.rand(nlines, LINE, generator=g, device=device) < 0.25
     ids = torch.where(sub, fresh, ids).reshape(-1)
     ntok = ids.numel()
     tl = lens[ids]

@@ -162,6 +162,56 @@ int dsg_pack_device(dsg_ctx *ctx, const dsg_entry *d_entries, size_t n, const ch
 /* Counters of the most recent dsg_pack* call on this context. */
 int dsg_get_stats(const dsg_ctx *ctx, dsg_stats *out);
 
+/* ---- host mirror of the Go call site (devspace_b200/csrc/hostpack.cc; host code only: walk, stat, read) ------ */
+
+/* fileInformation (pkg/devspace/sync/file_information.go:21-32) */
+typedef struct dsg_file_info {
+  const char *name;     /* Name: path relative to WatchPath ("" = the whole tree)                              */
+  int64_t size;         /* Size                                                                                */
+  int64_t mtime;        /* Mtime: seconds, rounded (roundMtime, util.go:87-89)                                 */
+  int32_t is_directory; /* IsDirectory                                                                         */
+  int32_t is_symlink;   /* IsSymbolicLink                                                                      */
+  int64_t remote_mode;  /* RemoteMode / RemoteUID / RemoteGID: replace Mode/Uid/Gid when the path is indexed   */
+  int64_t remote_uid;
+  int64_t remote_gid;
+} dsg_file_info;
+
+/* ignoreMatcher.MatchesPath / uploadIgnoreMatcher.MatchesPath (tar.go:196-206): non-zero = excluded */
+typedef int (*dsg_match_fn)(const char *relative_path, void *user);
+typedef void (*dsg_log_fn)(const char *line, void *user);
+
+/* The fields of SyncConfig that writeTar reads (sync_config.go): WatchPath, the two matchers, fileIndex.fileMap,
+ * Logf. retry_sleep_ms: the 4 s of tar.go:174 (0 = 4000); max_retries: 0 = retry forever like the reference. */
+typedef struct dsg_sync_config {
+  const char *watch_path;
+  dsg_match_fn ignore;
+  void *ignore_user;
+  dsg_match_fn upload_ignore;
+  void *upload_ignore_user;
+  const dsg_file_info *file_map;
+  size_t file_map_len;
+  dsg_log_fn log;
+  void *log_user;
+  uint32_t retry_sleep_ms;
+  uint32_t max_retries;
+} dsg_sync_config;
+
+typedef struct dsg_written dsg_written; /* writtenFiles + the manifest that was packed */
+
+/* recursiveTar / tarFolder / tarFile (tar.go:185-304) without the tar.Writer: the ordered header list and
+ * writtenFiles for a change list. Host only (no GPU). */
+int dsg_walk(const dsg_file_info *files, size_t nfiles, const dsg_sync_config *cfg, dsg_written **out);
+size_t dsg_written_count(const dsg_written *w);
+const dsg_file_info *dsg_written_get(const dsg_written *w, size_t i);
+const dsg_entry *dsg_written_entries(const dsg_written *w, size_t *n, const char **strtab, size_t *strtab_len,
+                                     uint64_t *arena_bytes);
+void dsg_written_free(dsg_written *w);
+
+/* writeTar (tar.go:146-182): temp file path in out_path, writtenFiles in *written; a failing walk / read is
+ * logged ("[Upstream] Tar failed: ..."), the temp file removed, and the whole call retried after the sleep. */
+int dsg_write_tar(dsg_ctx *ctx, const dsg_file_info *files, size_t nfiles, const dsg_sync_config *cfg, char *out_path,
+                  size_t out_path_cap, dsg_written **written);
+
 /* ---- single stages, device pointers (parity tests drive each kernel alone) ----------------------- */
 
 /* archive/tar Writer: headers + payload layout + padding + trailer into d_tar[tar_cap]. */
