@@ -57,6 +57,10 @@ __global__ void __launch_bounds__(1024) smem_kernel(uint32_t *out, long long *cy
       acc = reinterpret_cast<unsigned short *>(tab)[(acc + r) & (2 * kTable - 1)];
     } else if (MODE == 7) {  // random plain 16-bit store
       reinterpret_cast<unsigned short *>(tab)[r & (2 * kTable - 1)] = (unsigned short)r;
+    } else if (MODE == 9) {  // random atomicCAS 32-bit (exchange emulation, one attempt)
+      uint32_t *p = &tab[r & (kTable - 1)];
+      uint32_t old = *p;
+      acc += atomicCAS(p, old, r);
     } else if (MODE == 8) {  // shared atomicAdd histogram on 286 bins
       atomicAdd(&tab[r % 286u], 1u);
     }
@@ -140,6 +144,7 @@ int main() {
     run_smem<6>("lds16_dependent_chase", threads);
     run_smem<1>("atoms_exch32_random", threads);
     run_smem<2>("atoms_cas16_random", threads);
+    run_smem<9>("atoms_cas32_random", threads);
     run_smem<8>("atoms_add_hist286", threads);
     run_smem<3>("match_any_15bit", threads);
     run_smem<4>("match_any_3bit", threads);

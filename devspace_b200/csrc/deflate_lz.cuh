@@ -41,7 +41,7 @@
 
 namespace dsg {
 
-constexpr int kLzThreads = 512;
+constexpr int kLzThreads = 1024;
 constexpr int kLzWarps = kLzThreads / 32;
 constexpr int kChunk = 65536;
 constexpr int kTile = 8192;
@@ -87,8 +87,8 @@ struct LzLayout {
   static constexpr int cllen = dcode + 2 * 32;                    // u8[32]
   static constexpr int clcode = cllen + 32;                       // u16[32]
   static constexpr int rle = clcode + 2 * 32;                     // u16[320]
-  static constexpr int misc = rle + 2 * 320;                      // u32[64] scalars / scan scratch
-  static constexpr int huff = misc + 4 * 64 + 16;                 // 2 x HuffScratch + comb[512] + ctrl[80]
+  static constexpr int misc = rle + 2 * 320;                      // u32[192] scalars / scan scratch
+  static constexpr int huff = misc + 4 * 192 + 16;                 // 2 x HuffScratch + comb[512] + ctrl[80]
   static constexpr int total = huff + 2 * 4064 + 512 + 4 * 80 + 16;
 };
 static_assert(sizeof(HuffScratch) <= 4064, "HuffScratch grew");
@@ -99,7 +99,7 @@ static_assert(kMaxDist % 16 == 0 && kLook % 16 == 0, "ring loads move 16-byte gr
 
 // misc[] slots
 enum { kMTicket = 0, kMStart, kMNTok, kMMode, kMOutLo, kMOutHi, kMHdrBits, kMChunkBytes, kMHlit, kMHdist, kMHclen,
-       kMNRle, kMBodyDyn, kMBodyFix, kMError, kMScan = 32 /* 16 warp partials + carry */ };
+       kMNRle, kMBodyDyn, kMBodyFix, kMError, kMRunCtr, kMScan = 32 /* 16 warp partials + carry */ };
 
 // Kernel parameter block
 struct LzParams {
@@ -120,6 +120,25 @@ enum { kProfLoad = 0, kProfInsert, kProfSearch, kProfParse, kProfEmit, kProfHuff
 
 DSG_D uint32_t ring_slot(int rp /* run-relative position, >= -kDict */) {
   return (uint32_t)(rp + kDict) % (uint32_t)kRing;
+}
+
+// A thread group inside the CTA: all threads (barrier 0 = __syncthreads) or warps 1.. (named barrier 1), used to
+// overlap the single-warp parse of one tile with loading and hashing the next tile.
+struct LzGroup {
+  int tid;   // index inside the group
+  int n;     // threads in the group (multiple of 32)
+  int bar;   // 0 = the whole CTA
+};
+DSG_D void group_sync(const LzGroup &g) {
+  if (g.bar == 0) {
+    __syncthreads();
+  } else {
+#if defined(DSG_EMU)
+    emu::named_barrier_sync(g.bar, g.n);
+#else
+    asm volatile("bar.sync %0, %1;" ::"r"(g.bar), "r"(g.n) : "memory");
+#endif
+  }
 }
 
 DSG_D uint32_t hash4(uint32_t v) { return (v * 2654435761u) >> (32 - kHashBits); }
@@ -182,9 +201,9 @@ struct SmemBitWriter {
 
 // Copies stream bytes [g0, g1) (absolute offsets in the call's input, may be negative = dictionary from the
 // previous segment, may exceed len = zero fill) to the ring slots of chunk-relative positions rp0...
-DSG_D void load_ring(uint8_t *s_data, const LzParams &P, int64_t cs, int rp0, int rp1) {
+DSG_D void load_ring(uint8_t *s_data, const LzParams &P, int64_t cs, int rp0, int rp1, const LzGroup &g) {
   // 16-byte granules: rp0 and rp1 are multiples of 16 and the ring size is a multiple of 16
-  for (int rp = rp0 + 16 * (int)threadIdx.x; rp < rp1; rp += 16 * kLzThreads) {
+  for (int rp = rp0 + 16 * g.tid; rp < rp1; rp += 16 * g.n) {
     const int64_t g = cs + rp;
     uint4 v = make_uint4(0, 0, 0, 0);
     if (g >= 0 && g + 16 <= (int64_t)P.len && (((uintptr_t)(P.in + g)) & 15) == 0) {
@@ -212,7 +231,7 @@ DSG_D void load_ring(uint8_t *s_data, const LzParams &P, int64_t cs, int rp0, in
 }
 
 // Inserts positions [rp0, rp1) into the hash chains in EXACT stream order (nearest candidate first), 1024
-// positions per round, two per thread. Inside a round the threads race, so a thread does a lock-free sorted
+// positions per round, one per thread. Inside a round the threads race, so a thread does a lock-free sorted
 // insertion: it walks past entries of its own round that lie LATER in the stream (they can only be ahead by
 // < 1024 positions) and links itself below them with a compare-and-swap on the link it came through (32-bit
 // CAS on the head table, 16-bit CAS on a prev[] entry). Exact order matters: chains that are only ordered per
@@ -221,13 +240,15 @@ DSG_D void load_ring(uint8_t *s_data, const LzParams &P, int64_t cs, int rp0, in
 // them would land in the same bucket (quadratic walks, useless candidates); the search gives them the
 // distance-1 candidate directly. Their chain start is whatever the head holds when they look (an entry of the
 // same round that lies ahead of them is skipped by the search).
-constexpr int kInsRound = 2 * kLzThreads;
+constexpr int kInsRound = kLzThreads;
+constexpr int kInsWalkMax = 96;
 
 DSG_D void insert_one(const uint8_t *s_data, unsigned short *prev16, uint32_t *s_head, int rp, int lo_rp) {
   const uint32_t slot = ring_slot(rp);
   const uint32_t v = load4(s_data + slot);
   const uint32_t h = hash4(v);
-  if (rp > lo_rp && v == load4(s_data + ring_slot(rp - 1))) {  // interior of a byte run
+  // interior of a byte run: the five bytes p-1..p+3 are equal
+  if (rp > lo_rp && v == (v & 0xffu) * 0x01010101u && s_data[slot ? slot - 1 : kRing - 1] == (uint8_t)v) {
     prev16[slot] = (unsigned short)s_head[h];
     return;
   }
@@ -236,7 +257,9 @@ DSG_D void insert_one(const uint8_t *s_data, unsigned short *prev16, uint32_t *s
   int walked = 0;
   for (;;) {
     const uint32_t nxt = at_head ? s_head[holder] : (uint32_t)prev16[holder];
-    if (nxt != kNil && ++walked < 2 * kInsRound) {  // the bound only guards against stale links
+    // The bound guards against stale links: a slot of this round that has not been inserted yet still holds the
+    // link of the position that occupied it one ring lap ago, and such links can form cycles.
+    if (nxt != kNil && ++walked < kInsWalkMax) {
       int fwd = (int)nxt - (int)slot;
       if (fwd < 0) fwd += kRing;
       if (fwd > 0 && fwd < kInsRound) {  // an entry of this round that is later in the stream
@@ -259,13 +282,13 @@ DSG_D void insert_one(const uint8_t *s_data, unsigned short *prev16, uint32_t *s
   }
 }
 
-DSG_D void insert_positions(const uint8_t *s_data, uint16_t *s_prev, uint32_t *s_head, int rp0, int rp1, int lo_rp) {
+DSG_D void insert_positions(const uint8_t *s_data, uint16_t *s_prev, uint32_t *s_head, int rp0, int rp1, int lo_rp,
+                            const LzGroup &g) {
   unsigned short *prev16 = reinterpret_cast<unsigned short *>(s_prev);
-  for (int base = rp0; base < rp1; base += kInsRound) {
-    const int r0 = base + (int)threadIdx.x, r1 = r0 + kLzThreads;
+  for (int base = rp0; base < rp1; base += g.n) {  // g.n <= kInsRound positions per round
+    const int r0 = base + g.tid;
     if (r0 < rp1) insert_one(s_data, prev16, s_head, r0, lo_rp);
-    if (r1 < rp1) insert_one(s_data, prev16, s_head, r1, lo_rp);
-    __syncthreads();  // rounds are ordered
+    group_sync(g);  // rounds are ordered
   }
 }
 
@@ -278,6 +301,7 @@ DSG_D void insert_positions(const uint8_t *s_data, uint16_t *s_prev, uint32_t *s
 // 4-byte compare step, or finishes a position and sets up the next -- so the lanes of a warp never wait for
 // the lane with the longest chain or the longest compare.
 constexpr int kWays = 1;
+constexpr int kSearchRun = 8;  // positions per dynamically assigned run
 constexpr int kSubRun = kRun / kWays;
 
 struct SearchWay {
@@ -304,106 +328,140 @@ DSG_D void search_way_init(SearchWay &w, const uint8_t *s_data, int tile_rp, int
   else w.v_prev = ~load4(w.a);
 }
 
-DSG_D void search_way_step(SearchWay &w, const uint8_t *s_data, const uint16_t *s_prev, uint8_t *s_mlen,
-                           uint16_t *s_mdist, int tile_rp, int chunk_end, int lo_rp) {
-  enum { kSetup = 0, kWalk = 1, kCmp = 2 };
-  if (w.st == kSetup) {
-    const int rp = tile_rp + w.pos0 + w.j;
-    w.maxlen = chunk_end - rp < kMaxMatch ? chunk_end - rp : kMaxMatch;
-    w.best = 0;
-    w.bdist = 0;
-    w.depth = 0;
-    w.q = kNil;
-    w.last_d = 0;
-    w.skips = 0;
-    w.st = kWalk;
-    const uint32_t v = load4(w.a);
-    if (w.maxlen >= kMinMatch) {
-      if (w.inh_len > kMinMatch) {
-        w.best = w.inh_len - 1 < w.maxlen ? w.inh_len - 1 : w.maxlen;
-        w.bdist = w.inh_dist;
-      }
-      w.max_back = rp - lo_rp < kMaxDist ? rp - lo_rp : kMaxDist;
-      w.depth = w.best >= kNice ? 0 : (w.best >= kGood ? kDepth / 4 : kDepth);
-      w.q = s_prev[w.slot];
-      w.aw = load4(w.a + (w.best >= 3 ? w.best - 3 : 0));  // the four bytes a better match has to reproduce last
-      if (v == w.v_prev && w.max_back > 0 && w.best < kNice && !(w.bdist == 1 && w.best >= kMinMatch)) {
-        // interior of a byte run: try the distance-1 candidate (never in the chains, see insert_one)
-        w.cb = w.a - 1 + (w.slot == 0 ? kRing : 0);
-        w.cd = 1;
-        w.cl = 4;  // v == v_prev: the first four bytes are known to match
-        w.qn = w.q;
-        w.st = kCmp;
-      }
+// Sets up position w.j of the run (inheritance, window, chain start, byte-run candidate).
+DSG_D void search_way_setup(SearchWay &w, const uint8_t *s_data, const uint16_t *s_prev, int tile_rp, int chunk_end,
+                            int lo_rp) {
+  enum { kWalk = 1, kCmp = 2 };
+  const int rp = tile_rp + w.pos0 + w.j;
+  w.maxlen = chunk_end - rp < kMaxMatch ? chunk_end - rp : kMaxMatch;
+  w.best = 0;
+  w.bdist = 0;
+  w.depth = 0;
+  w.q = kNil;
+  w.last_d = 0;
+  w.skips = 0;
+  w.st = kWalk;
+  const uint32_t v = load4(w.a);
+  if (w.maxlen >= kMinMatch) {
+    if (w.inh_len > kMinMatch) {
+      w.best = w.inh_len - 1 < w.maxlen ? w.inh_len - 1 : w.maxlen;
+      w.bdist = w.inh_dist;
     }
-    w.v_prev = v;
-  } else if (w.st == kWalk) {
-    if (w.depth > 0 && w.q != kNil) {
-      w.depth--;
-      int d = (int)w.slot - (int)w.q;
-      if (d <= 0) d += kRing;
-      if (d > kRing - kInsRound && w.skips < 64) {
-        // the chain start of a run-interior position may be an entry of its own round that lies ahead
-        w.skips++;
-        w.depth++;
-        w.q = s_prev[w.q];
-      } else if (d > w.max_back || d <= w.last_d) {
-        w.q = kNil;  // left the window, or a stale link (chains are in exact stream order: distances grow)
-      } else {
-        w.last_d = d;
-        const uint8_t *b = s_data + w.q;
-        w.qn = s_prev[w.q];  // next link, fetched before the compare so that its latency overlaps
-        if (load4(b + (w.best >= 3 ? w.best - 3 : 0)) == w.aw) {
-          w.cb = b;
-          w.cd = d;
-          w.cl = 0;
-          w.st = kCmp;
-        } else {
-          w.q = w.qn;
-        }
-      }
+    w.max_back = rp - lo_rp < kMaxDist ? rp - lo_rp : kMaxDist;
+    w.depth = w.best >= kNice ? 0 : (w.best >= kGood ? kDepth / 4 : kDepth);
+    w.q = s_prev[w.slot];
+    w.aw = w.a[w.best];  // the byte a longer match has to reproduce (cheap first filter)
+    if (v == w.v_prev && w.max_back > 0 && w.best < kNice && !(w.bdist == 1 && w.best >= kMinMatch)) {
+      // interior of a byte run: try the distance-1 candidate (never in the chains, see insert_one)
+      w.cb = w.a - 1 + (w.slot == 0 ? kRing : 0);
+      w.cd = 1;
+      w.cl = 4;  // v == v_prev: the first four bytes are known to match
+      w.qn = w.q;
+      w.st = kCmp;
+    }
+  }
+  w.v_prev = v;
+}
+
+// The three actions of the per-lane state machine.
+DSG_D void search_cmp_step(SearchWay &w) {  // one 4-byte step of the candidate at distance cd
+  enum { kWalk = 1 };
+  const uint32_t x = w.cl < w.maxlen ? (load4(w.a + w.cl) ^ load4(w.cb + w.cl)) : 1u;
+  if (x == 0) {
+    w.cl += 4;
+    return;
+  }
+  int l = w.cl < w.maxlen ? w.cl + ((__ffs((int)x) - 1) >> 3) : w.maxlen;
+  if (l > w.maxlen) l = w.maxlen;
+  if (l >= kMinMatch && (l > w.best || (l == w.best && w.cd < w.bdist))) {
+    w.best = l;
+    w.bdist = w.cd;
+    if (l >= kNice || l >= w.maxlen) w.depth = 0;
+    else w.aw = w.a[l];
+  }
+  w.q = w.qn;
+  w.st = kWalk;
+}
+
+DSG_D void search_walk_step(SearchWay &w, const uint8_t *s_data, const uint16_t *s_prev) {  // one chain step
+  enum { kCmp = 2 };
+  w.depth--;
+  int d = (int)w.slot - (int)w.q;
+  if (d <= 0) d += kRing;
+  if (d > w.max_back || d <= w.last_d) {
+    if (d > kRing - kInsRound && w.skips < 64) {
+      // the chain start of a run-interior position may be an entry of its own round that lies ahead
+      w.skips++;
+      w.depth++;
+      w.q = s_prev[w.q];
     } else {
-      if (w.best < kMinMatch) w.best = 0;
-      s_mlen[w.pos0 + w.j] = (uint8_t)(w.best ? w.best - 3 : 0);  // 0 = no match, else len-3 in 1..255
-      s_mdist[w.pos0 + w.j] = (uint16_t)w.bdist;
-      w.inh_len = w.best;
-      w.inh_dist = w.bdist;
-      w.j++;
-      w.slot++;
-      w.a++;
-      if (w.slot == (uint32_t)kRing) {
-        w.slot = 0;
-        w.a = s_data;
-      }
-      w.st = kSetup;
+      w.q = kNil;  // left the window, or a stale link (chains are in exact stream order: distances grow)
     }
-  } else {  // kCmp: one 4-byte step of the candidate at distance cd
-    const uint32_t x = w.cl < w.maxlen ? (load4(w.a + w.cl) ^ load4(w.cb + w.cl)) : 1u;
-    if (x == 0) {
-      w.cl += 4;
-    } else {
-      int l = w.cl < w.maxlen ? w.cl + ((__ffs((int)x) - 1) >> 3) : w.maxlen;
-      if (l > w.maxlen) l = w.maxlen;
-      if (l >= kMinMatch && (l > w.best || (l == w.best && w.cd < w.bdist))) {
-        w.best = l;
-        w.bdist = w.cd;
-        if (l >= kNice || l >= w.maxlen) w.depth = 0;
-        else w.aw = load4(w.a + w.best - 3);
-      }
-      w.q = w.qn;
-      w.st = kWalk;
-    }
+    return;
+  }
+  w.last_d = d;
+  const uint8_t *b = s_data + w.q;
+  const uint32_t qn = s_prev[w.q];  // next link, fetched before the compare so that its latency overlaps
+  if (b[w.best] == (uint8_t)w.aw) {
+    w.qn = qn;
+    w.cb = b;
+    w.cd = d;
+    w.cl = 0;
+    w.st = kCmp;
+  } else {
+    w.q = qn;
   }
 }
 
+// Chain exhausted: record the position and set up the next one of the run (the caller hands out a new run).
+DSG_D void search_finish_position(SearchWay &w, const uint8_t *s_data, const uint16_t *s_prev, uint8_t *s_mlen,
+                                  uint16_t *s_mdist, int tile_rp, int chunk_end, int lo_rp) {
+  if (w.best < kMinMatch) w.best = 0;
+  s_mlen[w.pos0 + w.j] = (uint8_t)(w.best ? w.best - 3 : 0);  // 0 = no match, else len-3 in 1..255
+  s_mdist[w.pos0 + w.j] = (uint16_t)w.bdist;
+  w.inh_len = w.best;
+  w.inh_dist = w.bdist;
+  w.j++;
+  w.slot++;
+  w.a++;
+  if (w.slot == (uint32_t)kRing) {
+    w.slot = 0;
+    w.a = s_data;
+  }
+  if (w.j < kSearchRun) search_way_setup(w, s_data, s_prev, tile_rp, chunk_end, lo_rp);
+}
+
+// Positions are handed out in runs of kSearchRun through a shared-memory counter: a lane that finishes its run
+// takes the next free one while the other lanes of its warp keep walking, so neither lanes nor warps wait for the
+// slowest run at the barrier behind the search. Every iteration performs ONE action per lane (chain step,
+// 4-byte compare step, or finishing a position and setting up the next).
+// Measured alternatives that were slower on B200 (profiles/r01_lz_phases.md): fixed 16-position runs per
+// thread, two interleaved runs per thread, and warp-voted scheduling of the three actions.
+// `ctr` must be zero on entry.
 DSG_D void search_tile(const uint8_t *s_data, const uint16_t *s_prev, uint8_t *s_mlen, uint16_t *s_mdist, int tile_rp,
-                       int chunk_end, int lo_rp) {
-  const int t0 = (int)threadIdx.x * kRun;
-  // (two interleaved sub-runs per thread were measured slower than one: the kernel is bound by instruction
-  // issue at ~10 active lanes per warp, not by the latency of a single chain, profiles/r01_lz_phases.md)
-  SearchWay w0;
-  search_way_init(w0, s_data, tile_rp, t0, lo_rp);
-  while (w0.j < kSubRun) search_way_step(w0, s_data, s_prev, s_mlen, s_mdist, tile_rp, chunk_end, lo_rp);
+                       int tile_len, int chunk_end, int lo_rp, uint32_t *ctr) {
+  enum { kWalk = 1, kCmp = 2 };
+  const uint32_t nruns = (uint32_t)((tile_len + kSearchRun - 1) / kSearchRun);
+  SearchWay w;
+  uint32_t run = atomicAdd(ctr, 1u);
+  if (run >= nruns) return;
+  search_way_init(w, s_data, tile_rp, (int)run * kSearchRun, lo_rp);
+  search_way_setup(w, s_data, s_prev, tile_rp, chunk_end, lo_rp);
+  for (;;) {
+    if (w.st == kCmp) {
+      search_cmp_step(w);
+    } else if (w.depth > 0 && w.q != kNil) {
+      search_walk_step(w, s_data, s_prev);
+    } else {
+      search_finish_position(w, s_data, s_prev, s_mlen, s_mdist, tile_rp, chunk_end, lo_rp);
+      if (w.j >= kSearchRun) {
+        run = atomicAdd(ctr, 1u);
+        if (run >= nruns) break;
+        search_way_init(w, s_data, tile_rp, (int)run * kSearchRun, lo_rp);
+        search_way_setup(w, s_data, s_prev, tile_rp, chunk_end, lo_rp);
+      }
+    }
+  }
 }
 
 // next(p) for the stateless lazy parse; tp is tile-relative, tile_len = positions of this tile inside the chunk
@@ -658,9 +716,11 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
     for (uint32_t i = tid; i < (uint32_t)kHashSize; i += kLzThreads) s_head[i] = kNil;
     // dictionary + first tile + look-ahead are resident before the dictionary is hashed (the last three
     // dictionary positions hash over the first bytes of the run). kMaxDist is a multiple of 16.
-    load_ring(s_data, P, rs, -(((-lo_rp) + 15) & ~15), kTile + kLook);
+    const LzGroup g_all{(int)tid, kLzThreads, 0};
+    const LzGroup g_rest{(int)tid - 32, kLzThreads - 32, 1};  // everybody but warp 0
+    load_ring(s_data, P, rs, -(((-lo_rp) + 15) & ~15), kTile + kLook, g_all);
     __syncthreads();
-    insert_positions(s_data, s_prev, s_head, lo_rp, 0, lo_rp);
+    insert_positions(s_data, s_prev, s_head, lo_rp, 0, lo_rp, g_all);
     LZ_PROF(kProfLoad);
 
     for (uint32_t k = 0; k < R; k++) {
@@ -682,26 +742,39 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
     for (int t = 0; t < ntiles; t++) {
       const int tile_rp = crp + t * kTile;
       const int tile_len = chunk_len - t * kTile < kTile ? chunk_len - t * kTile : kTile;
-      if (tile_rp > 0) {  // next tile's bytes + look-ahead replace the oldest dictionary bytes
-        load_ring(s_data, P, rs, tile_rp + kLook, tile_rp + kTile + kLook);
-        __syncthreads();
+      if (t == 0) {  // first tile of the chunk: load (unless it came with the dictionary) and hash it with all threads
+        if (tile_rp > 0) {  // its bytes + look-ahead replace the oldest dictionary bytes
+          load_ring(s_data, P, rs, tile_rp + kLook, tile_rp + kTile + kLook, g_all);
+          __syncthreads();
+        }
+        LZ_PROF(kProfLoad);
+        insert_positions(s_data, s_prev, s_head, tile_rp, tile_rp + tile_len, lo_rp, g_all);  // ends with a barrier
+        LZ_PROF(kProfInsert);
       }
-      LZ_PROF(kProfLoad);
-      insert_positions(s_data, s_prev, s_head, tile_rp, tile_rp + tile_len, lo_rp);
-      LZ_PROF(kProfInsert);
-      search_tile(s_data, s_prev, s_mlen, s_mdist, tile_rp, crp + chunk_len, lo_rp);
+      if (tid == 0) s_misc[kMRunCtr] = 0;
+      __syncthreads();
+      search_tile(s_data, s_prev, s_mlen, s_mdist, tile_rp, tile_len, crp + chunk_len, lo_rp, &s_misc[kMRunCtr]);
       __syncthreads();
       LZ_PROF(kProfSearch);
+      // Warp 0 parses this tile (a latency-bound single-warp job) while the other 31 warps load and hash the next
+      // tile of the chunk: neither touches what the other reads (parse: match lengths + bitmap; load/insert: ring
+      // bytes older than this tile's window, head and prev tables).
       if (warp == 0) {
         const int nxt = parse_tile_warp0(s_mlen, s_bitmap, (int)s_misc[kMStart], tile_len);
         if (lane == 0) s_misc[kMStart] = (uint32_t)nxt;
+      } else if (t + 1 < ntiles) {
+        const int nrp = tile_rp + kTile;
+        const int nlen = chunk_len - (t + 1) * kTile < kTile ? chunk_len - (t + 1) * kTile : kTile;
+        load_ring(s_data, P, rs, nrp + kLook, nrp + kTile + kLook, g_rest);
+        group_sync(g_rest);
+        insert_positions(s_data, s_prev, s_head, nrp, nrp + nlen, lo_rp, g_rest);
       }
       __syncthreads();
       LZ_PROF(kProfParse);
       // emit tokens: rank of every start position, then token words + histograms
       {
         const int t0 = (int)tid * kRun;
-        const uint32_t bits = (s_bitmap[t0 >> 5] >> (t0 & 31)) & 0xffffu;
+        const uint32_t bits = (s_bitmap[t0 >> 5] >> (t0 & 31)) & ((1u << kRun) - 1u);
         uint32_t total;
         uint32_t rank = block_exclusive_scan((uint32_t)__popc(bits), s_misc + kMScan, &total);
         const uint32_t base = s_misc[kMNTok];
@@ -775,16 +848,16 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
         fix += __shfl_xor_sync(0xffffffffu, fix, o);
       }
       if (lane == 0) {
-        s_misc[kMScan + warp] = dyn;
-        s_misc[kMScan + 16 + warp] = fix;
+        s_misc[72 + warp] = dyn;
+        s_misc[112 + warp] = fix;
       }
     }
     __syncthreads();
     if (tid == 0) {
       uint32_t body_dyn = 0, body_fix = 0;
       for (int w = 0; w < kLzWarps; w++) {
-        body_dyn += s_misc[kMScan + w];
-        body_fix += s_misc[kMScan + 16 + w];
+        body_dyn += s_misc[72 + w];
+        body_fix += s_misc[112 + w];
       }
       // code-length code
       const uint32_t hlit = s_misc[kMHlit], hdist = s_misc[kMHdist];

@@ -71,6 +71,8 @@ struct BlockState {
   unsigned bar_arrived = 0;
   unsigned bar_gen = 0;
   int current = -1;
+  unsigned nb_arrived[16] = {0};
+  unsigned nb_gen[16] = {0};
   ucontext_t sched;
   std::function<void()> body;
   std::vector<unsigned char> dyn;
@@ -172,6 +174,18 @@ inline void launch(dim3 grid, dim3 block, size_t dyn_bytes, const std::function<
         }
         cur_block() = nullptr;
       }
+}
+
+// bar.sync id, count: `count` threads of the block rendezvous on barrier `id` (1..15)
+inline void named_barrier_sync(int id, int count) {
+  BlockState *b = cur_block();
+  const unsigned my_gen = b->nb_gen[id];
+  if (++b->nb_arrived[id] >= (unsigned)count) {
+    b->nb_arrived[id] = 0;
+    b->nb_gen[id]++;
+    return;
+  }
+  while (b->nb_gen[id] == my_gen) yield();
 }
 
 inline unsigned lane_id() { return (threadIdx.x + threadIdx.y * blockDim.x + threadIdx.z * blockDim.x * blockDim.y) & 31; }

@@ -25,6 +25,9 @@ def make_local_tree(local):
     for f in ("testFolder/testFile1", "testFolder/testFile2", "testFolder/ignoredFile", "ignoredFolder/testFile1"):
         (local / f).write_bytes(FILE_CONTENTS)
     os.chmod(local / "testFile2", 0o755)
+    for root, dirs, fs in os.walk(local):          # fixed, past mtimes: a header mtime rounded UP (WriteHeader) must
+        for n in dirs + fs:                        # not lie in the future when the remote tar extracts it
+            os.utime(os.path.join(root, n), ns=(1546300900_000000000, 1546300900_000000000))
     os.utime(local / "testFile1", ns=(1546300800_600000000, 1546300800_600000000))   # .6 s: rounds up
 
 
