@@ -53,7 +53,10 @@ constexpr int kHashBits = 13;
 constexpr int kHashSize = 1 << kHashBits;
 constexpr int kMinMatch = 4;
 constexpr int kMaxMatch = 258;
-constexpr int kDepth = 32;
+constexpr int kDepth = 8;          // first pass: every position, shallow
+constexpr int kDeepDepth = 160;    // second pass: token starts and their lazy successors only
+constexpr int kRefineRounds = 2;
+constexpr int kMaxCompares = 16;   // full compares per position
 constexpr int kNice = 128;
 constexpr int kGood = 8;
 constexpr int kRun = kTile / kLzThreads;  // 16 consecutive positions per thread
@@ -89,7 +92,9 @@ struct LzLayout {
   static constexpr int rle = clcode + 2 * 32;                     // u16[320]
   static constexpr int misc = rle + 2 * 320;                      // u32[192] scalars / scan scratch
   static constexpr int huff = misc + 4 * 192 + 16;                 // 2 x HuffScratch + comb[512] + ctrl[80]
-  static constexpr int total = huff + 2 * 4064 + 512 + 4 * 80 + 16;
+  static constexpr int work = huff + 2 * 4064 + 512 + 4 * 80 + 16; // u16[kTile] positions for the deep pass
+  static constexpr int deep = work + 2 * kTile;                    // u32[kTile/32] positions already searched deeply
+  static constexpr int total = deep + kTile / 8 + 16;
 };
 static_assert(sizeof(HuffScratch) <= 4064, "HuffScratch grew");
 static_assert(LzLayout::prev % 16 == 0 && LzLayout::head % 16 == 0 && LzLayout::mlen % 16 == 0, "alignment");
@@ -116,7 +121,8 @@ struct LzParams {
   unsigned long long *prof;   // optional: cycles per phase, summed over CTAs (thread 0's clock64 deltas)
 };
 
-enum { kProfLoad = 0, kProfInsert, kProfSearch, kProfParse, kProfEmit, kProfHuff, kProfSizes, kProfPack, kProfCount };
+enum { kProfLoad = 0, kProfInsert, kProfSearch, kProfParse, kProfEmit, kProfHuff, kProfSizes, kProfPack, kProfRefParse,
+       kProfRefList, kProfRefDeep, kProfCount };
 
 DSG_D uint32_t ring_slot(int rp /* run-relative position, >= -kDict */) {
   return (uint32_t)(rp + kDict) % (uint32_t)kRing;
@@ -307,7 +313,7 @@ constexpr int kSubRun = kRun / kWays;
 struct SearchWay {
   int j, st, pos0;  // position index inside the sub-run, state, tile-relative first position
   int inh_len, inh_dist;
-  int maxlen, best, bdist, depth, max_back, last_d, skips;
+  int maxlen, best, bdist, depth, max_back, last_d, skips, cmps;
   int cl, cd;  // compare state: bytes matched so far, distance of the candidate
   uint32_t slot, q, qn, aw, v_prev;
   const uint8_t *a, *cb;
@@ -318,7 +324,7 @@ DSG_D void search_way_init(SearchWay &w, const uint8_t *s_data, int tile_rp, int
   w.st = 0;
   w.pos0 = pos0;
   w.inh_len = w.inh_dist = 0;
-  w.maxlen = w.best = w.bdist = w.depth = w.max_back = w.last_d = w.skips = w.cl = w.cd = 0;
+  w.maxlen = w.best = w.bdist = w.depth = w.max_back = w.last_d = w.skips = w.cmps = w.cl = w.cd = 0;
   w.slot = ring_slot(tile_rp + pos0);
   w.q = w.qn = kNil;
   w.aw = 0;
@@ -340,6 +346,7 @@ DSG_D void search_way_setup(SearchWay &w, const uint8_t *s_data, const uint16_t 
   w.q = kNil;
   w.last_d = 0;
   w.skips = 0;
+  w.cmps = 0;
   w.st = kWalk;
   const uint32_t v = load4(w.a);
   if (w.maxlen >= kMinMatch) {
@@ -408,6 +415,9 @@ DSG_D void search_walk_step(SearchWay &w, const uint8_t *s_data, const uint16_t 
     w.cd = d;
     w.cl = 0;
     w.st = kCmp;
+    // Periodic data (records, tables) makes every candidate pass the one-byte filter and cost a full compare
+    // without ever getting longer: after kMaxCompares of them the position is done.
+    if (++w.cmps >= kMaxCompares) w.depth = 0;
   } else {
     w.q = qn;
   }
@@ -418,7 +428,9 @@ DSG_D void search_finish_position(SearchWay &w, const uint8_t *s_data, const uin
                                   uint16_t *s_mdist, int tile_rp, int chunk_end, int lo_rp) {
   if (w.best < kMinMatch) w.best = 0;
   s_mlen[w.pos0 + w.j] = (uint8_t)(w.best ? w.best - 3 : 0);  // 0 = no match, else len-3 in 1..255
-  s_mdist[w.pos0 + w.j] = (uint16_t)w.bdist;
+  // bit 15: the walk stopped at the depth limit with the chain unfinished -> worth a deep second look
+  const bool limited = w.q != kNil && w.best < kNice && w.best < w.maxlen && w.maxlen >= kMinMatch;
+  s_mdist[w.pos0 + w.j] = (uint16_t)(w.bdist | (limited ? 0x8000 : 0));
   w.inh_len = w.best;
   w.inh_dist = w.bdist;
   w.j++;
@@ -460,6 +472,108 @@ DSG_D void search_tile(const uint8_t *s_data, const uint16_t *s_prev, uint8_t *s
         search_way_init(w, s_data, tile_rp, (int)run * kSearchRun, lo_rp);
         search_way_setup(w, s_data, s_prev, tile_rp, chunk_end, lo_rp);
       }
+    }
+  }
+}
+
+// ---- second pass: deep search of the positions the parse actually uses ---------------------------------------
+// zlib spends its 128 chain steps only where a token starts (and at the byte behind a match start, for the lazy
+// decision); spending them at every position is what made the first version of this kernel slow, and a uniform
+// depth of 32 left 5-7 % of compression on the table for text. So: shallow pass everywhere, parse, then a deep
+// pass over the token starts + their successors (a compacted, well balanced work list), parse again.
+
+// Work list: the token starts of `bitmap` and, behind every start that carries a match, the next position --
+// each at most once per tile (s_deep). Returns the list length (all threads).
+DSG_D uint32_t refine_build_list(const uint8_t *s_mlen, const uint16_t *s_mdist, const uint32_t *s_bitmap,
+                                 uint32_t *s_deep, uint16_t *s_work, uint32_t *scan_scratch, int tile_len) {
+  const int t0 = (int)threadIdx.x * kRun;
+  uint16_t mine[2 * kRun];
+  uint32_t n = 0;
+  const uint32_t bits = (s_bitmap[t0 >> 5] >> (t0 & 31)) & ((1u << kRun) - 1u);
+  uint32_t m = bits;
+  while (m) {
+    const int j = __ffs((int)m) - 1;
+    m &= m - 1;
+    const int tp = t0 + j;
+    // only positions whose shallow walk ran into the depth limit (bit 15 of mdist) can gain anything
+    if ((s_mdist[tp] & 0x8000) && !(s_deep[tp >> 5] & (1u << (tp & 31)))) mine[n++] = (uint16_t)tp;
+    const int nx = tp + 1;
+    if (s_mlen[tp] != 0 && nx < tile_len && (s_mdist[nx] & 0x8000) && !(s_bitmap[nx >> 5] & (1u << (nx & 31))) &&
+        !(s_deep[nx >> 5] & (1u << (nx & 31))))
+      mine[n++] = (uint16_t)nx;
+  }
+  __syncthreads();  // every thread has read s_deep before anybody updates it
+  uint32_t total;
+  uint32_t at = block_exclusive_scan(n, scan_scratch, &total);
+  for (uint32_t k = 0; k < n; k++) {
+    s_work[at + k] = mine[k];
+    atomicOr(&s_deep[mine[k] >> 5], 1u << (mine[k] & 31));
+  }
+  __syncthreads();
+  return total;
+}
+
+// Deep search of the listed positions, handed out through a shared counter (`ctr` zero on entry). The walk is a
+// tight loop (the kernel is issue bound here: every instruction per chain step counts); the rare full compare is
+// done inline, 4 bytes per step.
+DSG_D void refine_search(const uint8_t *s_data, const uint16_t *s_prev, uint8_t *s_mlen, uint16_t *s_mdist,
+                         const uint16_t *s_work, uint32_t nwork, int tile_rp, int chunk_end, int lo_rp, uint32_t *ctr) {
+  for (;;) {
+    const uint32_t k = atomicAdd(ctr, 1u);
+    if (k >= nwork) break;
+    const int tp = s_work[k];
+    const int rp = tile_rp + tp;
+    const int slot = (int)ring_slot(rp);
+    const uint8_t *a = s_data + slot;
+    const int maxlen = chunk_end - rp < kMaxMatch ? chunk_end - rp : kMaxMatch;
+    const uint32_t cur = s_mlen[tp];
+    int best = cur ? (int)cur + 3 : 0;
+    int bdist = cur ? (int)(s_mdist[tp] & 0x7fff) : 0;
+    if (maxlen < kMinMatch || best >= kNice || best >= maxlen) continue;
+    const int max_back = rp - lo_rp < kMaxDist ? rp - lo_rp : kMaxDist;
+    // zlib: a quarter of the effort at the byte behind an already good match
+    int depth = (tp > 0 && s_mlen[tp - 1] != 0 && s_mlen[tp - 1] + 3u >= (uint32_t)kGood) ? kDeepDepth / 4 : kDeepDepth;
+    int cmps = kMaxCompares;
+    int last_d = 0;
+    uint32_t q = s_prev[slot];
+    uint8_t want = a[best];
+    while (depth > 0 && q != kNil) {
+      int d = slot - (int)q;
+      if (d <= 0) d += kRing;
+      if (d > max_back || d <= last_d) {
+        if (d <= kRing - kInsRound) break;  // left the window, or a stale link
+        q = s_prev[q];                      // an entry of the same insertion round that lies ahead: skip it
+        depth--;
+        continue;
+      }
+      last_d = d;
+      depth--;
+      const uint8_t *b = s_data + q;
+      const uint32_t qn = s_prev[q];
+      if (b[best] == want) {
+        int l = 0;
+        while (l < maxlen) {
+          const uint32_t x = load4(a + l) ^ load4(b + l);
+          if (x) {
+            l += (__ffs((int)x) - 1) >> 3;
+            break;
+          }
+          l += 4;
+        }
+        if (l > maxlen) l = maxlen;
+        if (l > best) {
+          best = l;
+          bdist = d;
+          if (l >= kNice || l >= maxlen) break;
+          want = a[best];
+        }
+        if (--cmps == 0) break;  // periodic data: every candidate passes the filter and none gets longer
+      }
+      q = qn;
+    }
+    if (best >= kMinMatch) {
+      s_mlen[tp] = (uint8_t)(best - 3);
+      s_mdist[tp] = (uint16_t)bdist;
     }
   }
 }
@@ -515,43 +629,51 @@ DSG_D int parse_tile_warp0(const uint8_t *s_mlen, uint32_t *s_bitmap, int start,
     }
     if (cur) bm[widx] = cur;
   }
-  const int exit_p = p;  // first token start at or beyond the end of the sub-range
-  // serial fix-up by lane 0 over the 32 sub-ranges (exits travel through shared memory: no shuffle / warp
-  // barrier per sub-range): a sub-range whose true entry equals its speculated entry keeps its marks.
+  // Fix-up, all lanes in parallel: a lane whose true entry (its left neighbour's exit) differs from the entry its
+  // marks were made for re-walks from the true entry until it meets a position that is already marked -- from
+  // there on the old marks are the right ones (next() is stateless) and its exit does not change. Exits travel
+  // through shared memory. The pass is repeated while some exit changed (rarely more than twice: a re-walk that
+  // does not converge inside its 256 positions changes the neighbour's entry).
   uint32_t *s_exit = s_bitmap + kTile / 32;  // 32 words behind the bitmap
-  s_exit[lane] = (uint32_t)exit_p;
+  int my_exit = p;                             // first token start at or beyond the end of the sub-range
+  int used = lane == 0 ? start : sub_lo;       // the entry the current marks belong to
+  s_exit[lane] = (uint32_t)my_exit;
   __syncwarp();
-  int result = 0;
-  if (lane == 0) {
-    int true_in = (int)s_exit[0];  // sub-range 0 was parsed from the true start
-    for (int l = 1; l < 32; l++) {
-      const int lo = l * kSub;
-      if (lo >= tile_len) break;  // nothing beyond the tile
-      const int hi = (lo + kSub < tile_len) ? lo + kSub : tile_len;
-      if (true_in == lo) {
-        true_in = (int)s_exit[l];  // speculation was right
-      } else if (true_in >= hi) {
-        clear_bits(bm, lo, hi);  // the whole sub-range lies inside an earlier match
+  for (int pass = 0; pass < 33; pass++) {
+    const int e = lane == 0 ? used : (int)s_exit[lane - 1];
+    bool changed = false;
+    if (lane > 0 && e != used) {
+      const int old_exit = my_exit;
+      if (sub_lo >= tile_len || e >= sub_hi) {
+        if (sub_lo < tile_len) clear_bits(bm, sub_lo, sub_hi);  // the whole sub-range lies inside an earlier match
+        my_exit = e;
       } else {
-        clear_bits(bm, lo, true_in);
-        int q = true_in;
+        clear_bits(bm, sub_lo, e);
+        int q = e;
         bool converged = false;
-        while (q < hi) {
+        while (q < sub_hi) {
           if (bm[q >> 5] & (1u << (q & 31))) {
             converged = true;
             break;
           }
           bm[q >> 5] |= 1u << (q & 31);
           const int nq = q + parse_step(s_mlen, q, tile_len);
-          clear_bits(bm, q + 1, nq < hi ? nq : hi);
+          clear_bits(bm, q + 1, nq < sub_hi ? nq : sub_hi);
           q = nq;
         }
-        true_in = converged ? (int)s_exit[l] : q;
+        if (!converged) my_exit = q;
+        else if (my_exit < sub_hi) my_exit = q;  // cannot happen: a marked path always has an exit >= sub_hi
       }
+      used = e;
+      changed = my_exit != old_exit;
     }
-    result = true_in - tile_len;  // >= 0: first token start of the following tile, relative to it
+    __syncwarp();
+    s_exit[lane] = (uint32_t)my_exit;
+    __syncwarp();
+    if (!__any_sync(0xffffffffu, changed)) break;
   }
-  return __shfl_sync(0xffffffffu, result, 0);
+  const int last_exit = __shfl_sync(0xffffffffu, my_exit, 31);
+  return last_exit - tile_len;  // >= 0: first token start of the following tile, relative to it
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -686,6 +808,8 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
   uint16_t *s_clcode = reinterpret_cast<uint16_t *>(smem + LzLayout::clcode);
   uint16_t *s_rle = reinterpret_cast<uint16_t *>(smem + LzLayout::rle);
   uint32_t *s_misc = reinterpret_cast<uint32_t *>(smem + LzLayout::misc);
+  uint16_t *s_work = reinterpret_cast<uint16_t *>(smem + LzLayout::work);
+  uint32_t *s_deep = reinterpret_cast<uint32_t *>(smem + LzLayout::deep);
   uint32_t *s_stage = reinterpret_cast<uint32_t *>(smem + LzLayout::mlen);  // bit-packing window (after the tiles)
   uint32_t *tokens = P.tok_scratch + (size_t)blockIdx.x * kTokSlotWords;
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -756,9 +880,21 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
       search_tile(s_data, s_prev, s_mlen, s_mdist, tile_rp, tile_len, crp + chunk_len, lo_rp, &s_misc[kMRunCtr]);
       __syncthreads();
       LZ_PROF(kProfSearch);
+      // refine: parse, deep-search the token starts and their successors, repeat
+      for (uint32_t i = tid; i < (uint32_t)kTile / 32; i += kLzThreads) s_deep[i] = 0;
+      for (int r = 0; r < kRefineRounds; r++) {
+        if (warp == 0) parse_tile_warp0(s_mlen, s_bitmap, (int)s_misc[kMStart], tile_len);
+        if (tid == 0) s_misc[kMRunCtr] = 0;
+        __syncthreads();
+        LZ_PROF(kProfRefParse);
+        const uint32_t nwork = refine_build_list(s_mlen, s_mdist, s_bitmap, s_deep, s_work, s_misc + kMScan, tile_len);
+        LZ_PROF(kProfRefList);
+        refine_search(s_data, s_prev, s_mlen, s_mdist, s_work, nwork, tile_rp, crp + chunk_len, lo_rp,
+                      &s_misc[kMRunCtr]);
+        __syncthreads();
+        LZ_PROF(kProfRefDeep);
+      }
       // Warp 0 parses this tile (a latency-bound single-warp job) while the other 31 warps load and hash the next
-      // tile of the chunk: neither touches what the other reads (parse: match lengths + bitmap; load/insert: ring
-      // bytes older than this tile's window, head and prev tables).
       if (warp == 0) {
         const int nxt = parse_tile_warp0(s_mlen, s_bitmap, (int)s_misc[kMStart], tile_len);
         if (lane == 0) s_misc[kMStart] = (uint32_t)nxt;
@@ -791,7 +927,7 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
             tok = s_data[ring_slot(tile_rp + tp)];
             atomicAdd(&s_lfreq[tok], 1u);
           } else {
-            const uint32_t d = s_mdist[tp];
+            const uint32_t d = s_mdist[tp] & 0x7fffu;
             tok = kTokMatch | (l << 16) | (d - 1);  // l = len-3
             atomicAdd(&s_lfreq[257 + len_code(l + 3)], 1u);
             atomicAdd(&s_dfreq[dist_code(d)], 1u);
