@@ -123,13 +123,10 @@ def test_level6_deflate_roundtrip(packer6, name):
     assert len(raw) <= len(data) + 10 * ((len(data) + 65535) // 65536) + 2       # never worse than stored chunks
 
 
-# Judged equality (3): compressed size <= 1.03 x the oracle's zlib level-6 size. The bound holds on the
-# real files of BASELINE config 1 and on the ELF-like binary mix of config 4 (the bench workload). The synthetic
-# JS-like token text is the one known outlier: its vocabulary makes every 4-gram recur hundreds of times inside the
-# 32 KiB window, so the best match sits deeper in the hash chain than this kernel looks (depth 32; zlib level 6 looks
-# 128 deep) -- measured 1.05-1.07, asserted at 1.09 and documented in DESIGN.md as open work (real source trees:
-# within 1-2 %, tools/lzmodel.cc on site-packages tarballs).
-SIZE_CASES = {"elf_like_binary": 1.03, "c1_quickstart": 1.03, "js_like_text": 1.09}
+# Judged equality (3): compressed size <= 1.03 x the oracle's zlib level-6 size. Measured on the B200
+# (tools/size_ratios.py): ELF-like binary 1.0004, BASELINE config 1 0.9961, JS-like token text 1.0228 (the hardest
+# case: every 4-gram recurs hundreds of times per 32 KiB window; it needs the deep second search pass).
+SIZE_CASES = {"elf_like_binary": 1.03, "c1_quickstart": 1.03, "js_like_text": 1.03}
 
 
 @pytest.mark.parametrize("name", sorted(SIZE_CASES))
@@ -185,7 +182,8 @@ def test_level6_pipeline_segments_share_one_member(tmp_path):
 
 def test_level6_small_trees_size_vs_oracle(packer6):
     from devspace_b200 import synth
-    for man, bound in ((synth.tree_c2(3000, 12_000_000), 1.09), (synth.tree_c4(2, 6 << 20), 1.03)):
+    for man, bound in ((synth.tree_c2(3000, 12_000_000), 1.03), (synth.tree_c3(200, 40_000_000), 1.03),
+                       (synth.tree_c4(2, 6 << 20), 1.03)):
         out = packer6.pack(man)
         tar = gzip.decompress(out)
         # the tar stream itself is checked against the oracle through the generic path
