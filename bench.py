@@ -139,6 +139,11 @@ def cpu_pack_seconds(es):
     return time.perf_counter() - t0, len(tar), n
 
 
+def workload_name(files, fbytes):
+    return (f"C4 build context shard: {files} files x {fbytes >> 20} MiB ELF-like binaries per GPU "
+            f"(N=8 x 32 files = the 256-file / 64 GiB config)")
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return 0
@@ -174,8 +179,10 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "C4 build context: 256 MiB-class ELF-like binaries, file sharded",
-                   "files_per_step": files, "file_bytes": file_bytes, "level": 6},
+        "config": {"workload": workload_name(args.files, args.file_bytes), "files_per_gpu": args.files,
+                   "file_bytes": args.file_bytes, "level": 6,
+                   "sample": f"bounded sample of that workload: {files} files x {file_bytes >> 20} MiB of the same "
+                             "generator per step, one file per host thread"},
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
                          "sample": f"{files} files x {file_bytes >> 20} MiB per step, one file per host thread; "
                                    "CPU restatement of archive/tar + gzip (zlib level 6), Go toolchain absent"},
@@ -343,8 +350,7 @@ def main():
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": t_res * 1e3 / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8", "data": "synthetic",
-        "config": {"workload": f"C4 build context shard: {files} files x {fbytes >> 20} MiB ELF-like binaries per GPU "
-                               f"(N=8 x 32 files = the 256-file / 64 GiB config)", "files_per_gpu": files,
+        "config": {"workload": workload_name(files, fbytes), "files_per_gpu": files,
                    "file_bytes": fbytes, "level": 6, "payload_bytes_per_gpu": P, "tar_bytes_per_gpu": T,
                    "gzip_bytes_per_gpu": out_bytes, "l2": "inputs (>= 8 GiB per step) far exceed the 126 MB L2",
                    "timing": "value: CUDA events in libdsgpack (dsg_stats.ms_total), max over ranks; e2e: wall clock "
