@@ -53,7 +53,7 @@ constexpr int kHashBits = 13;
 constexpr int kHashSize = 1 << kHashBits;
 constexpr int kMinMatch = 4;
 constexpr int kMaxMatch = 258;
-constexpr int kDepth = 8;          // first pass: every position, shallow
+constexpr int kDepth = 4;          // first pass: every position, shallow
 constexpr int kDeepDepth = 160;    // second pass: token starts and their lazy successors only
 constexpr int kRefineRounds = 2;
 constexpr int kMaxCompares = 16;   // full compares per position
@@ -122,7 +122,9 @@ struct LzParams {
 };
 
 enum { kProfLoad = 0, kProfInsert, kProfSearch, kProfParse, kProfEmit, kProfHuff, kProfSizes, kProfPack, kProfRefParse,
-       kProfRefList, kProfRefDeep, kProfCount };
+       kProfRefList, kProfRefDeep, kProfCount,
+       // not phases: sum over warps of (own finish - phase start) / 32, to tell the tail of a phase from its bulk
+       kProfWarpSearch = kProfCount, kProfWarpDeep, kProfSlots };
 
 DSG_D uint32_t ring_slot(int rp /* run-relative position, >= -kDict */) {
   return (uint32_t)(rp + kDict) % (uint32_t)kRing;
@@ -146,6 +148,13 @@ DSG_D void group_sync(const LzGroup &g) {
 #endif
   }
 }
+
+#if defined(DSG_EMU) && defined(DSG_EMU_STATS)
+extern "C" unsigned long long g_dsg_stat[16];
+#define DSG_STAT(i, v) (g_dsg_stat[i] += (v))
+#else
+#define DSG_STAT(i, v) ((void)0)
+#endif
 
 DSG_D uint32_t hash4(uint32_t v) { return (v * 2654435761u) >> (32 - kHashBits); }
 
@@ -393,6 +402,7 @@ DSG_D void search_cmp_step(SearchWay &w) {  // one 4-byte step of the candidate 
 DSG_D void search_walk_step(SearchWay &w, const uint8_t *s_data, const uint16_t *s_prev) {  // one chain step
   enum { kCmp = 2 };
   w.depth--;
+  DSG_STAT(2, 1);
   int d = (int)w.slot - (int)w.q;
   if (d <= 0) d += kRing;
   if (d > w.max_back || d <= w.last_d) {
@@ -518,10 +528,12 @@ DSG_D uint32_t refine_build_list(const uint8_t *s_mlen, const uint16_t *s_mdist,
 // done inline, 4 bytes per step.
 DSG_D void refine_search(const uint8_t *s_data, const uint16_t *s_prev, uint8_t *s_mlen, uint16_t *s_mdist,
                          const uint16_t *s_work, uint32_t nwork, int tile_rp, int chunk_end, int lo_rp, uint32_t *ctr) {
+  if (threadIdx.x == 0) DSG_STAT(3, 1);
   for (;;) {
     const uint32_t k = atomicAdd(ctr, 1u);
     if (k >= nwork) break;
     const int tp = s_work[k];
+    DSG_STAT(0, 1);
     const int rp = tile_rp + tp;
     const int slot = (int)ring_slot(rp);
     const uint8_t *a = s_data + slot;
@@ -548,6 +560,7 @@ DSG_D void refine_search(const uint8_t *s_data, const uint16_t *s_prev, uint8_t 
       }
       last_d = d;
       depth--;
+      DSG_STAT(1, 1);
       const uint8_t *b = s_data + q;
       const uint32_t qn = s_prev[q];
       if (b[best] == want) {
@@ -674,6 +687,107 @@ DSG_D int parse_tile_warp0(const uint8_t *s_mlen, uint32_t *s_bitmap, int start,
   }
   const int last_exit = __shfl_sync(0xffffffffu, my_exit, 31);
   return last_exit - tile_len;  // >= 0: first token start of the following tile, relative to it
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Wide parse: the same marks as parse_tile_warp0, computed by kParseWarps warps. Every lane owns ONE bitmap word
+// (32 positions) and keeps it in a register; a warp owns a segment of 1024 positions.
+//   1. every lane walks speculatively from the start of its word (the very first lane: from `start`);
+//   2. inside a warp the exits travel by shuffle: a lane whose true entry (its left neighbour's exit) differs from
+//      the entry its marks were made for re-walks until it meets a marked position (next() is stateless, so from
+//      there on the old marks and the old exit stand); repeated until no exit of the warp changes;
+//   3. the segment exits travel through shared memory the same way, until no segment exit changes.
+// Called by the first kParseThreads threads; `bar` is a named barrier for exactly those threads.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kParseWarps = kTile / 1024;
+constexpr int kParseThreads = kParseWarps * 32;
+
+// Re-walk of one word from entry e (>= sub_lo). Returns the new exit, or -1 when the walk met the marked path.
+DSG_D int parse_lane_walk(const uint8_t *s_mlen, uint32_t &cur, int e, int sub_lo, int sub_hi, int tile_len) {
+  if (e >= sub_hi) {  // the whole word lies inside an earlier match (or beyond the tile)
+    cur = 0;
+    return e;
+  }
+  cur &= ~((1u << (e - sub_lo)) - 1u);
+  int q = e;
+  while (q < sub_hi) {
+    const int b = q - sub_lo;
+    if ((cur >> b) & 1u) return -1;
+    if ((q & 3) == 0 && q + 4 <= sub_hi && ((cur >> b) & 0xfu) == 0u &&
+        *reinterpret_cast<const uint32_t *>(s_mlen + q) == 0u) {  // four literals in a row
+      cur |= 0xfu << b;
+      q += 4;
+      continue;
+    }
+    cur |= 1u << b;
+    const int nq = q + parse_step(s_mlen, q, tile_len);
+    const int hi = (nq < sub_hi ? nq : sub_hi) - sub_lo;  // clear the marks the token covers: bits (b, hi)
+    const uint32_t upto_hi = hi >= 32 ? 0xffffffffu : ((1u << hi) - 1u);
+    const uint32_t upto_b = (2u << b) - 1u;               // bits [0, b]
+    cur &= ~(upto_hi & ~upto_b);
+    q = nq;
+  }
+  return q;
+}
+
+// In-warp fixed point; seg_entry = the entry of the warp's first lane. Returns this lane's exit.
+DSG_D int parse_warp_settle(const uint8_t *s_mlen, uint32_t &cur, int &used, int ex, int seg_entry, int sub_lo,
+                            int sub_hi, int tile_len) {
+  const int lane = (int)(threadIdx.x & 31);
+  for (int pass = 0; pass < 34; pass++) {
+    const int left = __shfl_up_sync(0xffffffffu, ex, 1);
+    const int e = lane == 0 ? seg_entry : left;
+    bool changed = false;
+    if (e != used) {
+      const int r = parse_lane_walk(s_mlen, cur, e, sub_lo, sub_hi, tile_len);
+      if (r >= 0) {
+        changed = r != ex;
+        ex = r;
+      }
+      used = e;
+    }
+    if (!__any_sync(0xffffffffu, changed)) break;
+  }
+  return ex;
+}
+
+DSG_D int parse_tile_wide(const uint8_t *s_mlen, uint32_t *s_bitmap, int start, int tile_len, int bar) {
+  const int g = (int)threadIdx.x;  // 0 .. kParseThreads-1
+  const int lane = g & 31, w = g >> 5;
+  const int sub_lo = g * 32;
+  const int sub_hi = sub_lo + 32 < tile_len ? sub_lo + 32 : tile_len;
+  uint32_t *s_x = s_bitmap + kTile / 32;  // [0, kParseWarps): segment exits; [kParseWarps, +2): change flags
+  const LzGroup grp{g, kParseThreads, bar};
+  uint32_t cur = 0;
+  int seg_entry = w == 0 ? start : w * 1024;
+  int used = lane == 0 ? seg_entry : sub_lo;
+  int ex = parse_lane_walk(s_mlen, cur, used, sub_lo, sub_hi, tile_len);
+  ex = parse_warp_settle(s_mlen, cur, used, ex, seg_entry, sub_lo, sub_hi, tile_len);
+  if (lane == 31) s_x[w] = (uint32_t)ex;
+  if (g == 0) {
+    s_x[kParseWarps] = 0;
+    s_x[kParseWarps + 1] = 0;
+  }
+  for (int round = 0; round < kParseWarps + 1; round++) {
+    uint32_t *flag = s_x + kParseWarps + (round & 1);
+    group_sync(grp);  // exits and the cleared flag are visible
+    const int e = w == 0 ? start : (int)s_x[w - 1];
+    bool changed = false;
+    if (e != seg_entry) {
+      seg_entry = e;
+      const int old = ex;
+      ex = parse_warp_settle(s_mlen, cur, used, ex, seg_entry, sub_lo, sub_hi, tile_len);
+      changed = lane == 31 && ex != old;
+    }
+    if (changed) *flag = 1u;
+    group_sync(grp);  // every exit has been read, every flag written
+    if (lane == 31) s_x[w] = (uint32_t)ex;
+    if (g == 0) s_x[kParseWarps + ((round + 1) & 1)] = 0;
+    if (*flag == 0u) break;
+  }
+  s_bitmap[g] = cur;
+  group_sync(grp);
+  return (int)s_x[kParseWarps - 1] - tile_len;  // >= 0: first token start of the following tile, relative to it
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -841,7 +955,7 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
     // dictionary + first tile + look-ahead are resident before the dictionary is hashed (the last three
     // dictionary positions hash over the first bytes of the run). kMaxDist is a multiple of 16.
     const LzGroup g_all{(int)tid, kLzThreads, 0};
-    const LzGroup g_rest{(int)tid - 32, kLzThreads - 32, 1};  // everybody but warp 0
+    const LzGroup g_rest{(int)tid - kParseThreads, kLzThreads - kParseThreads, 1};  // everybody but the parse warps
     load_ring(s_data, P, rs, -(((-lo_rp) + 15) & ~15), kTile + kLook, g_all);
     __syncthreads();
     insert_positions(s_data, s_prev, s_head, lo_rp, 0, lo_rp, g_all);
@@ -877,27 +991,31 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
       }
       if (tid == 0) s_misc[kMRunCtr] = 0;
       __syncthreads();
+      const long long t_ws = P.prof ? clock64() : 0;
       search_tile(s_data, s_prev, s_mlen, s_mdist, tile_rp, tile_len, crp + chunk_len, lo_rp, &s_misc[kMRunCtr]);
+      if (P.prof && lane == 0) atomicAdd(&P.prof[kProfWarpSearch], (unsigned long long)(clock64() - t_ws) / 32);
       __syncthreads();
       LZ_PROF(kProfSearch);
       // refine: parse, deep-search the token starts and their successors, repeat
       for (uint32_t i = tid; i < (uint32_t)kTile / 32; i += kLzThreads) s_deep[i] = 0;
       for (int r = 0; r < kRefineRounds; r++) {
-        if (warp == 0) parse_tile_warp0(s_mlen, s_bitmap, (int)s_misc[kMStart], tile_len);
+        if (warp < (uint32_t)kParseWarps) parse_tile_wide(s_mlen, s_bitmap, (int)s_misc[kMStart], tile_len, 2);
         if (tid == 0) s_misc[kMRunCtr] = 0;
         __syncthreads();
         LZ_PROF(kProfRefParse);
         const uint32_t nwork = refine_build_list(s_mlen, s_mdist, s_bitmap, s_deep, s_work, s_misc + kMScan, tile_len);
         LZ_PROF(kProfRefList);
+        const long long t_wd = P.prof ? clock64() : 0;
         refine_search(s_data, s_prev, s_mlen, s_mdist, s_work, nwork, tile_rp, crp + chunk_len, lo_rp,
                       &s_misc[kMRunCtr]);
+        if (P.prof && lane == 0) atomicAdd(&P.prof[kProfWarpDeep], (unsigned long long)(clock64() - t_wd) / 32);
         __syncthreads();
         LZ_PROF(kProfRefDeep);
       }
       // Warp 0 parses this tile (a latency-bound single-warp job) while the other 31 warps load and hash the next
-      if (warp == 0) {
-        const int nxt = parse_tile_warp0(s_mlen, s_bitmap, (int)s_misc[kMStart], tile_len);
-        if (lane == 0) s_misc[kMStart] = (uint32_t)nxt;
+      if (warp < (uint32_t)kParseWarps) {
+        const int nxt = parse_tile_wide(s_mlen, s_bitmap, (int)s_misc[kMStart], tile_len, 2);
+        if (tid == 0) s_misc[kMStart] = (uint32_t)nxt;
       } else if (t + 1 < ntiles) {
         const int nrp = tile_rp + kTile;
         const int nlen = chunk_len - (t + 1) * kTile < kTile ? chunk_len - (t + 1) * kTile : kTile;

@@ -358,8 +358,8 @@ int lz_launch(dsg_ctx *ctx, cudaStream_t stream, const uint8_t *d_in, uint64_t l
   P.prof = nullptr;
   static const bool prof_on = getenv("DSG_LZ_PROF") != nullptr;  // development aid: per-phase cycle counts on stderr
   if (prof_on) {
-    CU(ctx->lz_prof.ensure(sizeof(unsigned long long) * kProfCount));
-    CU(cudaMemsetAsync(ctx->lz_prof.p, 0, sizeof(unsigned long long) * kProfCount, stream));
+    CU(ctx->lz_prof.ensure(sizeof(unsigned long long) * kProfSlots));
+    CU(cudaMemsetAsync(ctx->lz_prof.p, 0, sizeof(unsigned long long) * kProfSlots, stream));
     P.prof = ctx->lz_prof.as<unsigned long long>();
   }
   lz_deflate_kernel<<<grid, kLzThreads, LzLayout::total, stream>>>(P);
@@ -369,7 +369,7 @@ int lz_launch(dsg_ctx *ctx, cudaStream_t stream, const uint8_t *d_in, uint64_t l
   lz_gather_kernel<<<nchunks, 256, 0, stream>>>(d_in, len, P.slots, meta, offs, nchunks, d_out, write_terminator, d_error);
   LAUNCH_CHECK();
   if (prof_on) {
-    unsigned long long h[kProfCount];
+    unsigned long long h[kProfSlots];
     CU(cudaMemcpyAsync(h, P.prof, sizeof h, cudaMemcpyDeviceToHost, stream));
     CU(cudaStreamSynchronize(stream));
     static const char *names[kProfCount] = {"load", "insert", "search", "parse", "emit", "huffman", "sizes", "pack",
@@ -378,7 +378,8 @@ int lz_launch(dsg_ctx *ctx, cudaStream_t stream, const uint8_t *d_in, uint64_t l
     for (int i = 0; i < kProfCount; i++) tot += h[i];
     fprintf(stderr, "[lz prof] chunks=%u grid=%u cycles/chunk:", nchunks, grid);
     for (int i = 0; i < kProfCount; i++) fprintf(stderr, " %s=%llu", names[i], h[i] / nchunks);
-    fprintf(stderr, " total=%llu\n", tot / nchunks);
+    fprintf(stderr, " total=%llu (mean warp finish: search=%llu ref_deep=%llu)\n", tot / nchunks,
+            h[kProfWarpSearch] / nchunks, h[kProfWarpDeep] / nchunks);
   }
   return DSG_OK;
 }
