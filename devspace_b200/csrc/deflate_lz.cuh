@@ -44,9 +44,12 @@ namespace dsg {
 constexpr int kLzThreads = 1024;
 constexpr int kLzWarps = kLzThreads / 32;
 constexpr int kChunk = 65536;
-constexpr int kTile = 8192;
+constexpr int kTeams = 2;                // the CTA works as two teams of 16 warps on alternate tiles (see the kernel)
+constexpr int kTeamThreads = kLzThreads / kTeams;
+constexpr int kTeamWarps = kTeamThreads / 32;
+constexpr int kTile = 4096;
 constexpr int kDict = 32768;
-constexpr int kRing = kDict + kTile;     // 40960 ring slots (bytes)
+constexpr int kRing = kDict + kTeams * kTile;  // 40960 ring slots (bytes): the window + one tile per team
 constexpr int kLook = 272;               // look-ahead beyond a tile (>= 258 + 3, multiple of 16)
 constexpr int kMaxDist = kDict - kLook;  // 32496
 constexpr int kHashBits = 13;
@@ -59,8 +62,7 @@ constexpr int kRefineRounds = 2;
 constexpr int kMaxCompares = 16;   // full compares per position
 constexpr int kNice = 128;
 constexpr int kGood = 8;
-constexpr int kRun = kTile / kLzThreads;  // 16 consecutive positions per thread
-constexpr int kSub = kTile / 32;          // 256 positions per parse lane
+constexpr int kRun = kTile / kTeamThreads;  // 8 consecutive positions per thread (list building, token emission)
 constexpr uint16_t kNil = 0xffff;
 constexpr int kStageBytes = 16384;        // bit-packing window
 constexpr int kBatchTokens = 2048;        // tokens per bit-packing batch (<= 48 bits each = 12 KiB)
@@ -78,10 +80,10 @@ struct LzLayout {
   static constexpr int data = 0;                                  // kRing + kLook + 48 bytes (mirror + slack)
   static constexpr int prev = data + kRing + kLook + 48;          // u16[kRing]
   static constexpr int head = prev + 2 * kRing;                   // u32[kHashSize]
-  static constexpr int mlen = head + 4 * kHashSize;               // u8[kTile]      } reused as the bit-packing
-  static constexpr int mdist = mlen + kTile;                      // u16[kTile]     } window after the last tile
-  static constexpr int bitmap = mdist + 2 * kTile;                // u32[kTile/32] token-start flags
-  static constexpr int lfreq = bitmap + kTile / 8 + 128;          // u32[288] (32 parse exits sit behind the bitmap)
+  static constexpr int mlen = head + 4 * kHashSize;               // u8[kTeams][kTile]   } reused as the bit-packing
+  static constexpr int mdist = mlen + kTeams * kTile;             // u16[kTeams][kTile]  } window after the last tile
+  static constexpr int bitmap = mdist + 2 * kTeams * kTile;       // u32[kTeams][kTile/32 + 16] token-start flags + exits
+  static constexpr int lfreq = bitmap + kTeams * (kTile / 8 + 64); // u32[288]
   static constexpr int dfreq = lfreq + 4 * 288;                   // u32[32]
   static constexpr int llen = dfreq + 4 * 32;                     // u8[288] literal/length code lengths
   static constexpr int dlen = llen + 288;                         // u8[32]
@@ -92,19 +94,21 @@ struct LzLayout {
   static constexpr int rle = clcode + 2 * 32;                     // u16[320]
   static constexpr int misc = rle + 2 * 320;                      // u32[192] scalars / scan scratch
   static constexpr int huff = misc + 4 * 192 + 16;                 // 2 x HuffScratch + comb[512] + ctrl[80]
-  static constexpr int work = huff + 2 * 4064 + 512 + 4 * 80 + 16; // u16[kTile] positions for the deep pass
-  static constexpr int deep = work + 2 * kTile;                    // u32[kTile/32] positions already searched deeply
-  static constexpr int total = deep + kTile / 8 + 16;
+  static constexpr int work = huff + 2 * 4064 + 512 + 4 * 80 + 16; // u16[kTeams][kTile] positions for the deep pass
+  static constexpr int deep = work + 2 * kTeams * kTile;           // u32[kTeams][kTile/32] positions searched deeply
+  static constexpr int total = deep + kTeams * kTile / 8 + 16;
 };
 static_assert(sizeof(HuffScratch) <= 4064, "HuffScratch grew");
 static_assert(LzLayout::prev % 16 == 0 && LzLayout::head % 16 == 0 && LzLayout::mlen % 16 == 0, "alignment");
-static_assert(kTile + 2 * kTile >= kStageBytes, "bit-packing window must fit in the match arrays");
+static_assert(kTeams * 3 * kTile >= kStageBytes, "bit-packing window must fit in the match arrays");
 static_assert(LzLayout::total <= 227 * 1024, "shared memory budget");
 static_assert(kMaxDist % 16 == 0 && kLook % 16 == 0, "ring loads move 16-byte granules");
 
 // misc[] slots
 enum { kMTicket = 0, kMStart, kMNTok, kMMode, kMOutLo, kMOutHi, kMHdrBits, kMChunkBytes, kMHlit, kMHdist, kMHclen,
-       kMNRle, kMBodyDyn, kMBodyFix, kMError, kMRunCtr, kMScan = 32 /* 16 warp partials + carry */ };
+       kMNRle, kMBodyDyn, kMBodyFix, kMError, kMRunCtr /* one per team */, kMRunCtr1,
+       kMScan = 32 /* CTA scan: 32 warp partials + carry; team scans: 20 words each */, kMTeamScan = kMScan,
+       kMTeamScanStride = 20 };
 
 // Kernel parameter block
 struct LzParams {
@@ -122,9 +126,13 @@ struct LzParams {
 };
 
 enum { kProfLoad = 0, kProfInsert, kProfSearch, kProfParse, kProfEmit, kProfHuff, kProfSizes, kProfPack, kProfRefParse,
-       kProfRefList, kProfRefDeep, kProfCount,
+       kProfRefList, kProfRefDeep, kProfWaitA, kProfWaitB, kProfJoin, kProfCount,
        // not phases: sum over warps of (own finish - phase start) / 32, to tell the tail of a phase from its bulk
        kProfWarpSearch = kProfCount, kProfWarpDeep, kProfSlots };
+
+// named barriers: 0 = the CTA
+enum { kBarTeam = 1 /* +team */, kBarInsert = 3 /* +producing team */, kBarEmit = 5 /* +producing team */,
+       kBarParse = 7 /* +team */ };
 
 DSG_D uint32_t ring_slot(int rp /* run-relative position, >= -kDict */) {
   return (uint32_t)(rp + kDict) % (uint32_t)kRing;
@@ -149,12 +157,23 @@ DSG_D void group_sync(const LzGroup &g) {
   }
 }
 
-#if defined(DSG_EMU) && defined(DSG_EMU_STATS)
-extern "C" unsigned long long g_dsg_stat[16];
-#define DSG_STAT(i, v) (g_dsg_stat[i] += (v))
+// Producer/consumer hand-off between the two teams on a named barrier: the producing team arrives (does not wait),
+// the consuming team waits; the barrier completes when all kLzThreads threads have done one or the other.
+DSG_D void handoff_arrive(int bar) {
+  __threadfence_block();
+#if defined(DSG_EMU)
+  emu::named_barrier_arrive(bar, kLzThreads);
 #else
-#define DSG_STAT(i, v) ((void)0)
+  asm volatile("bar.arrive %0, %1;" ::"r"(bar), "r"(kLzThreads) : "memory");
 #endif
+}
+DSG_D void handoff_wait(int bar) {
+#if defined(DSG_EMU)
+  emu::named_barrier_sync(bar, kLzThreads);
+#else
+  asm volatile("bar.sync %0, %1;" ::"r"(bar), "r"(kLzThreads) : "memory");
+#endif
+}
 
 DSG_D uint32_t hash4(uint32_t v) { return (v * 2654435761u) >> (32 - kHashBits); }
 
@@ -194,6 +213,34 @@ DSG_D uint32_t block_exclusive_scan(uint32_t v, uint32_t *scratch, uint32_t *tot
   __syncthreads();
   uint32_t r = scratch[warp] + (x - v);
   *total = scratch[kLzWarps];
+  return r;
+}
+
+// The same scan over the threads of a group (a team: 16 warps, its own named barrier). `scratch` >= 17 words.
+DSG_D uint32_t group_exclusive_scan(uint32_t v, uint32_t *scratch, uint32_t *total, const LzGroup &g) {
+  const uint32_t lane = (uint32_t)g.tid & 31, warp = (uint32_t)g.tid >> 5, nw = (uint32_t)g.n >> 5;
+  uint32_t x = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= (uint32_t)o) x += y;
+  }
+  if (lane == 31) scratch[warp] = x;
+  group_sync(g);
+  if (warp == 0) {
+    uint32_t t = lane < nw ? scratch[lane] : 0;
+    uint32_t s = t;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t y = __shfl_up_sync(0xffffffffu, s, o);
+      if (lane >= (uint32_t)o) s += y;
+    }
+    if (lane < nw) scratch[lane] = s - t;
+    if (lane == nw - 1) scratch[nw] = s;
+  }
+  group_sync(g);
+  uint32_t r = scratch[warp] + (x - v);
+  *total = scratch[nw];
   return r;
 }
 
@@ -300,7 +347,7 @@ DSG_D void insert_one(const uint8_t *s_data, unsigned short *prev16, uint32_t *s
 DSG_D void insert_positions(const uint8_t *s_data, uint16_t *s_prev, uint32_t *s_head, int rp0, int rp1, int lo_rp,
                             const LzGroup &g) {
   unsigned short *prev16 = reinterpret_cast<unsigned short *>(s_prev);
-  for (int base = rp0; base < rp1; base += g.n) {  // g.n <= kInsRound positions per round
+  for (int base = rp0; base < rp1; base += g.n) {  // g.n <= kInsRound positions per round (two per thread: slower)
     const int r0 = base + g.tid;
     if (r0 < rp1) insert_one(s_data, prev16, s_head, r0, lo_rp);
     group_sync(g);  // rounds are ordered
@@ -402,7 +449,6 @@ DSG_D void search_cmp_step(SearchWay &w) {  // one 4-byte step of the candidate 
 DSG_D void search_walk_step(SearchWay &w, const uint8_t *s_data, const uint16_t *s_prev) {  // one chain step
   enum { kCmp = 2 };
   w.depth--;
-  DSG_STAT(2, 1);
   int d = (int)w.slot - (int)w.q;
   if (d <= 0) d += kRing;
   if (d > w.max_back || d <= w.last_d) {
@@ -495,45 +541,67 @@ DSG_D void search_tile(const uint8_t *s_data, const uint16_t *s_prev, uint8_t *s
 // Work list: the token starts of `bitmap` and, behind every start that carries a match, the next position --
 // each at most once per tile (s_deep). Returns the list length (all threads).
 DSG_D uint32_t refine_build_list(const uint8_t *s_mlen, const uint16_t *s_mdist, const uint32_t *s_bitmap,
-                                 uint32_t *s_deep, uint16_t *s_work, uint32_t *scan_scratch, int tile_len) {
-  const int t0 = (int)threadIdx.x * kRun;
+                                 uint32_t *s_deep, uint16_t *s_work, uint32_t *scan_scratch, int tile_len,
+                                 const LzGroup &g) {
+  const int t0 = g.tid * kRun;
   uint16_t mine[2 * kRun];
-  uint32_t n = 0;
+  uint32_t n = 0, nfull = 0;
   const uint32_t bits = (s_bitmap[t0 >> 5] >> (t0 & 31)) & ((1u << kRun) - 1u);
+  // zlib spends a quarter of the effort at the byte behind an already good match. The class is decided here, from
+  // the state before the round (not while other lanes update their neighbours), and travels in bit 15.
+  auto quarter = [&](int tp) -> uint32_t {
+    return (tp > 0 && s_mlen[tp - 1] != 0 && s_mlen[tp - 1] + 3u >= (uint32_t)kGood) ? 0x8000u : 0u;
+  };
   uint32_t m = bits;
   while (m) {
     const int j = __ffs((int)m) - 1;
     m &= m - 1;
     const int tp = t0 + j;
     // only positions whose shallow walk ran into the depth limit (bit 15 of mdist) can gain anything
-    if ((s_mdist[tp] & 0x8000) && !(s_deep[tp >> 5] & (1u << (tp & 31)))) mine[n++] = (uint16_t)tp;
+    if ((s_mdist[tp] & 0x8000) && !(s_deep[tp >> 5] & (1u << (tp & 31)))) {
+      const uint32_t q = quarter(tp);
+      mine[n++] = (uint16_t)(tp | q);
+      nfull += q ? 0 : 1;
+    }
     const int nx = tp + 1;
     if (s_mlen[tp] != 0 && nx < tile_len && (s_mdist[nx] & 0x8000) && !(s_bitmap[nx >> 5] & (1u << (nx & 31))) &&
-        !(s_deep[nx >> 5] & (1u << (nx & 31))))
-      mine[n++] = (uint16_t)nx;
+        !(s_deep[nx >> 5] & (1u << (nx & 31)))) {
+      const uint32_t q = quarter(nx);
+      mine[n++] = (uint16_t)(nx | q);
+      nfull += q ? 0 : 1;
+    }
   }
-  __syncthreads();  // every thread has read s_deep before anybody updates it
+  group_sync(g);  // every thread has read s_deep before anybody updates it
+  // The full-depth positions go to the front of the list and the quarter-depth ones behind them: the lanes of a warp
+  // take 32 consecutive entries and wait for the longest walk among them, so walks of one length belong together,
+  // and the long ones start first. One scan carries both counts.
   uint32_t total;
-  uint32_t at = block_exclusive_scan(n, scan_scratch, &total);
+  const uint32_t at = group_exclusive_scan(nfull | ((n - nfull) << 16), scan_scratch, &total, g);
+  uint32_t at_full = at & 0xffffu, at_quarter = (total & 0xffffu) + (at >> 16);
   for (uint32_t k = 0; k < n; k++) {
-    s_work[at + k] = mine[k];
-    atomicOr(&s_deep[mine[k] >> 5], 1u << (mine[k] & 31));
+    const uint32_t tp = mine[k] & 0x7fffu;
+    if (mine[k] & 0x8000u) s_work[at_quarter++] = mine[k];
+    else s_work[at_full++] = mine[k];
+    atomicOr(&s_deep[tp >> 5], 1u << (tp & 31));
   }
-  __syncthreads();
-  return total;
+  group_sync(g);
+  return (total & 0xffffu) + (total >> 16);
 }
 
-// Deep search of the listed positions, handed out through a shared counter (`ctr` zero on entry). The walk is a
-// tight loop (the kernel is issue bound here: every instruction per chain step counts); the rare full compare is
-// done inline, 4 bytes per step.
+// Deep search of the listed positions, handed out through a shared counter (`ctr` zero on entry).
+// The walk is bound by the latency of one lane's chain of dependent shared-memory loads (the stall samples are
+// fixed-latency waits and scoreboard waits, not issue contention), so the links are chased kChase ahead: the loads
+// of prev[] depend only on each other, the filter bytes and the window checks of the candidates then overlap.
+// Speculative links past the end of a chain are kNil or stale slots: both are valid shared-memory indices.
+constexpr int kChase = 4;
+
 DSG_D void refine_search(const uint8_t *s_data, const uint16_t *s_prev, uint8_t *s_mlen, uint16_t *s_mdist,
                          const uint16_t *s_work, uint32_t nwork, int tile_rp, int chunk_end, int lo_rp, uint32_t *ctr) {
-  if (threadIdx.x == 0) DSG_STAT(3, 1);
   for (;;) {
     const uint32_t k = atomicAdd(ctr, 1u);
     if (k >= nwork) break;
-    const int tp = s_work[k];
-    DSG_STAT(0, 1);
+    const uint32_t item = s_work[k];
+    const int tp = (int)(item & 0x7fffu);
     const int rp = tile_rp + tp;
     const int slot = (int)ring_slot(rp);
     const uint8_t *a = s_data + slot;
@@ -543,46 +611,72 @@ DSG_D void refine_search(const uint8_t *s_data, const uint16_t *s_prev, uint8_t 
     int bdist = cur ? (int)(s_mdist[tp] & 0x7fff) : 0;
     if (maxlen < kMinMatch || best >= kNice || best >= maxlen) continue;
     const int max_back = rp - lo_rp < kMaxDist ? rp - lo_rp : kMaxDist;
-    // zlib: a quarter of the effort at the byte behind an already good match
-    int depth = (tp > 0 && s_mlen[tp - 1] != 0 && s_mlen[tp - 1] + 3u >= (uint32_t)kGood) ? kDeepDepth / 4 : kDeepDepth;
+    int depth = (item & 0x8000u) ? kDeepDepth / 4 : kDeepDepth;  // see refine_build_list
     int cmps = kMaxCompares;
     int last_d = 0;
     uint32_t q = s_prev[slot];
-    uint8_t want = a[best];
+    uint32_t want = a[best];
     while (depth > 0 && q != kNil) {
-      int d = slot - (int)q;
-      if (d <= 0) d += kRing;
-      if (d > max_back || d <= last_d) {
-        if (d <= kRing - kInsRound) break;  // left the window, or a stale link
-        q = s_prev[q];                      // an entry of the same insertion round that lies ahead: skip it
-        depth--;
-        continue;
-      }
-      last_d = d;
-      depth--;
-      DSG_STAT(1, 1);
-      const uint8_t *b = s_data + q;
-      const uint32_t qn = s_prev[q];
-      if (b[best] == want) {
-        int l = 0;
-        while (l < maxlen) {
-          const uint32_t x = load4(a + l) ^ load4(b + l);
-          if (x) {
-            l += (__ffs((int)x) - 1) >> 3;
-            break;
+      uint32_t c[kChase + 1];
+      c[0] = q;
+#pragma unroll
+      for (int i = 0; i < kChase; i++) c[i + 1] = c[i] == kNil ? (uint32_t)kNil : (uint32_t)s_prev[c[i]];
+      uint32_t f[kChase];
+#pragma unroll
+      for (int i = 0; i < kChase; i++) f[i] = s_data[(c[i] == kNil ? 0u : c[i]) + best];
+      bool stop = false;
+      uint32_t nq = c[kChase];
+#pragma unroll
+      for (int i = 0; i < kChase; i++) {
+        if (!stop) {
+          const uint32_t ci = c[i];
+          if (ci == kNil || depth <= 0) {
+            stop = true;
+            nq = kNil;
+          } else {
+            int d = slot - (int)ci;
+            if (d <= 0) d += kRing;
+            depth--;
+            if (d > max_back || d <= last_d) {
+              if (d <= kRing - kInsRound) {  // left the window, or a stale link
+                stop = true;
+                nq = kNil;
+              }                              // else: an entry of the same insertion round that lies ahead: skip it
+            } else {
+              last_d = d;
+              if (f[i] == want) {
+                const uint8_t *b = s_data + ci;
+                int l = 0;
+                while (l < maxlen) {
+                  const uint32_t x = load4(a + l) ^ load4(b + l);
+                  if (x) {
+                    l += (__ffs((int)x) - 1) >> 3;
+                    break;
+                  }
+                  l += 4;
+                }
+                if (l > maxlen) l = maxlen;
+                if (l > best) {
+                  best = l;
+                  bdist = d;
+                  stop = true;  // the filter bytes of the remaining candidates were read for the old length
+                  if (l >= kNice || l >= maxlen) {
+                    nq = kNil;
+                  } else {
+                    want = a[best];
+                    nq = c[i + 1];
+                  }
+                }
+                if (--cmps == 0) {  // periodic data: every candidate passes the filter and none gets longer
+                  stop = true;
+                  nq = kNil;
+                }
+              }
+            }
           }
-          l += 4;
         }
-        if (l > maxlen) l = maxlen;
-        if (l > best) {
-          best = l;
-          bdist = d;
-          if (l >= kNice || l >= maxlen) break;
-          want = a[best];
-        }
-        if (--cmps == 0) break;  // periodic data: every candidate passes the filter and none gets longer
       }
-      q = qn;
+      q = nq;
     }
     if (best >= kMinMatch) {
       s_mlen[tp] = (uint8_t)(best - 3);
@@ -599,105 +693,17 @@ DSG_D int parse_step(const uint8_t *s_mlen, int tp, int tile_len) {
   return (int)l + 3;
 }
 
-DSG_D void clear_bits(uint32_t *bm, int lo, int hi) {  // clears bits [lo, hi)
-  for (int p = lo; p < hi;) {
-    const int w = p >> 5, b = p & 31;
-    const int n = (32 - b) < (hi - p) ? (32 - b) : (hi - p);
-    const uint32_t mask = (n == 32 ? 0xffffffffu : ((1u << n) - 1u)) << b;
-    bm[w] &= ~mask;
-    p += n;
-  }
-}
-
-// Marks the token start positions of the tile in s_bitmap. `start` = first token start (tile-relative, may
-// lie beyond the tile). Returns the first token start of the following tile (relative to that tile).
-// Executed by warp 0 only.
-DSG_D int parse_tile_warp0(const uint8_t *s_mlen, uint32_t *s_bitmap, int start, int tile_len) {
-  const int lane = (int)(threadIdx.x & 31);
-  const int sub_lo = lane * kSub;
-  const int sub_hi = (sub_lo + kSub < tile_len) ? sub_lo + kSub : tile_len;
-  uint32_t *bm = s_bitmap;  // each lane owns words [lane*8, lane*8+8)
-  for (int w = 0; w < kSub / 32; w++) bm[lane * (kSub / 32) + w] = 0;
-  // speculative walk from the sub-range start (lane 0: from the true start). The current bitmap word is kept
-  // in a register; four literals in a row (the common case in incompressible data) are taken in one step.
-  int p = lane == 0 ? start : sub_lo;
-  {
-    int widx = p >> 5;
-    uint32_t cur = 0;
-    while (p < sub_hi) {
-      const int wi = p >> 5;
-      if (wi != widx) {
-        bm[widx] = cur;
-        widx = wi;
-        cur = 0;
-      }
-      if ((p & 3) == 0 && p + 4 <= sub_hi && p + 4 < tile_len &&
-          *reinterpret_cast<const uint32_t *>(s_mlen + p) == 0u) {
-        cur |= 0xfu << (p & 31);
-        p += 4;
-        continue;
-      }
-      cur |= 1u << (p & 31);
-      p += parse_step(s_mlen, p, tile_len);
-    }
-    if (cur) bm[widx] = cur;
-  }
-  // Fix-up, all lanes in parallel: a lane whose true entry (its left neighbour's exit) differs from the entry its
-  // marks were made for re-walks from the true entry until it meets a position that is already marked -- from
-  // there on the old marks are the right ones (next() is stateless) and its exit does not change. Exits travel
-  // through shared memory. The pass is repeated while some exit changed (rarely more than twice: a re-walk that
-  // does not converge inside its 256 positions changes the neighbour's entry).
-  uint32_t *s_exit = s_bitmap + kTile / 32;  // 32 words behind the bitmap
-  int my_exit = p;                             // first token start at or beyond the end of the sub-range
-  int used = lane == 0 ? start : sub_lo;       // the entry the current marks belong to
-  s_exit[lane] = (uint32_t)my_exit;
-  __syncwarp();
-  for (int pass = 0; pass < 33; pass++) {
-    const int e = lane == 0 ? used : (int)s_exit[lane - 1];
-    bool changed = false;
-    if (lane > 0 && e != used) {
-      const int old_exit = my_exit;
-      if (sub_lo >= tile_len || e >= sub_hi) {
-        if (sub_lo < tile_len) clear_bits(bm, sub_lo, sub_hi);  // the whole sub-range lies inside an earlier match
-        my_exit = e;
-      } else {
-        clear_bits(bm, sub_lo, e);
-        int q = e;
-        bool converged = false;
-        while (q < sub_hi) {
-          if (bm[q >> 5] & (1u << (q & 31))) {
-            converged = true;
-            break;
-          }
-          bm[q >> 5] |= 1u << (q & 31);
-          const int nq = q + parse_step(s_mlen, q, tile_len);
-          clear_bits(bm, q + 1, nq < sub_hi ? nq : sub_hi);
-          q = nq;
-        }
-        if (!converged) my_exit = q;
-        else if (my_exit < sub_hi) my_exit = q;  // cannot happen: a marked path always has an exit >= sub_hi
-      }
-      used = e;
-      changed = my_exit != old_exit;
-    }
-    __syncwarp();
-    s_exit[lane] = (uint32_t)my_exit;
-    __syncwarp();
-    if (!__any_sync(0xffffffffu, changed)) break;
-  }
-  const int last_exit = __shfl_sync(0xffffffffu, my_exit, 31);
-  return last_exit - tile_len;  // >= 0: first token start of the following tile, relative to it
-}
-
 // ---------------------------------------------------------------------------------------------------------
-// Wide parse: the same marks as parse_tile_warp0, computed by kParseWarps warps. Every lane owns ONE bitmap word
+// Parse of one tile: marks the token start positions in s_bitmap, computed by kParseWarps warps. `start` = first
+// token start (tile-relative, may lie beyond the tile). Every lane owns ONE bitmap word
 // (32 positions) and keeps it in a register; a warp owns a segment of 1024 positions.
 //   1. every lane walks speculatively from the start of its word (the very first lane: from `start`);
 //   2. inside a warp the exits travel by shuffle: a lane whose true entry (its left neighbour's exit) differs from
 //      the entry its marks were made for re-walks until it meets a marked position (next() is stateless, so from
 //      there on the old marks and the old exit stand); repeated until no exit of the warp changes;
 //   3. the segment exits travel through shared memory the same way, until no segment exit changes.
-// Called by the first kParseThreads threads; `bar` is a named barrier for exactly those threads.
+// Called by the first kParseThreads threads of a team (gtid = index inside the team); `bar` is a named barrier
+// for exactly those threads. Returns the first token start of the following tile, relative to that tile.
 // ---------------------------------------------------------------------------------------------------------
 constexpr int kParseWarps = kTile / 1024;
 constexpr int kParseThreads = kParseWarps * 32;
@@ -751,8 +757,8 @@ DSG_D int parse_warp_settle(const uint8_t *s_mlen, uint32_t &cur, int &used, int
   return ex;
 }
 
-DSG_D int parse_tile_wide(const uint8_t *s_mlen, uint32_t *s_bitmap, int start, int tile_len, int bar) {
-  const int g = (int)threadIdx.x;  // 0 .. kParseThreads-1
+DSG_D int parse_tile_wide(const uint8_t *s_mlen, uint32_t *s_bitmap, int start, int tile_len, int gtid, int bar) {
+  const int g = gtid;  // 0 .. kParseThreads-1
   const int lane = g & 31, w = g >> 5;
   const int sub_lo = g * 32;
   const int sub_hi = sub_lo + 32 < tile_len ? sub_lo + 32 : tile_len;
@@ -927,6 +933,16 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
   uint32_t *s_stage = reinterpret_cast<uint32_t *>(smem + LzLayout::mlen);  // bit-packing window (after the tiles)
   uint32_t *tokens = P.tok_scratch + (size_t)blockIdx.x * kTokSlotWords;
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  // the team's private arrays
+  const uint32_t team = warp / kTeamWarps;
+  const LzGroup g_team{(int)(tid - team * kTeamThreads), kTeamThreads, kBarTeam + (int)team};
+  uint8_t *t_mlen = s_mlen + team * kTile;
+  uint16_t *t_mdist = s_mdist + team * kTile;
+  uint32_t *t_bitmap = s_bitmap + team * (kTile / 32 + 16);
+  uint16_t *t_work = s_work + team * kTile;
+  uint32_t *t_deep = s_deep + team * (kTile / 32);
+  uint32_t *t_scan = s_misc + kMTeamScan + team * kMTeamScanStride;
+  uint32_t *t_ctr = s_misc + kMRunCtr + team;
 
   long long t_last = 0;
 #define LZ_PROF(k)                                                    \
@@ -955,7 +971,6 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
     // dictionary + first tile + look-ahead are resident before the dictionary is hashed (the last three
     // dictionary positions hash over the first bytes of the run). kMaxDist is a multiple of 16.
     const LzGroup g_all{(int)tid, kLzThreads, 0};
-    const LzGroup g_rest{(int)tid - kParseThreads, kLzThreads - kParseThreads, 1};  // everybody but the parse warps
     load_ring(s_data, P, rs, -(((-lo_rp) + 15) & ~15), kTile + kLook, g_all);
     __syncthreads();
     insert_positions(s_data, s_prev, s_head, lo_rp, 0, lo_rp, g_all);
@@ -976,88 +991,103 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
     }
     __syncthreads();
 
+    // ---- tiles: a two-stage pipeline over two teams -----------------------------------------------------------
+    // Team k (16 warps) owns the tiles t = k, k+2, ...; for each it runs stage A (load, hash, shallow search) and
+    // stage B (parse / deep search rounds, final parse, token emission). Hashing must follow the hashing of tile
+    // t-1 and stage B the emission of tile t-1 (token order, the carried parse position), both done by the other
+    // team: two hand-off barriers per direction. So while one team is in stage B of tile t the other is in stage A
+    // of tile t+1, and the long tails of the search phases (the last few chains of a tile: 40 % of the phase with
+    // one tile in flight) are filled with the other team's work. The ring holds the 32 KiB window plus both tiles:
+    // loading tile t+1 overwrites only bytes that lie beyond the window of every position of tile t.
     const int ntiles = (chunk_len + kTile - 1) / kTile;
-    for (int t = 0; t < ntiles; t++) {
+    for (int t = (int)team; t < ntiles; t += kTeams) {
       const int tile_rp = crp + t * kTile;
       const int tile_len = chunk_len - t * kTile < kTile ? chunk_len - t * kTile : kTile;
-      if (t == 0) {  // first tile of the chunk: load (unless it came with the dictionary) and hash it with all threads
-        if (tile_rp > 0) {  // its bytes + look-ahead replace the oldest dictionary bytes
-          load_ring(s_data, P, rs, tile_rp + kLook, tile_rp + kTile + kLook, g_all);
-          __syncthreads();
-        }
-        LZ_PROF(kProfLoad);
-        insert_positions(s_data, s_prev, s_head, tile_rp, tile_rp + tile_len, lo_rp, g_all);  // ends with a barrier
-        LZ_PROF(kProfInsert);
+      const bool has_next = t + 1 < ntiles;
+      // -- stage A
+      if (t > 0) handoff_wait(kBarInsert + (int)(team ^ 1u));  // tile t-1 is in the chains
+      LZ_PROF(kProfWaitA);
+      if (tile_rp > 0) {  // (the first tile of a run came with the dictionary) its bytes + look-ahead replace the oldest
+        load_ring(s_data, P, rs, tile_rp + kLook, tile_rp + kTile + kLook, g_team);
+        group_sync(g_team);
       }
-      if (tid == 0) s_misc[kMRunCtr] = 0;
-      __syncthreads();
+      LZ_PROF(kProfLoad);
+      insert_positions(s_data, s_prev, s_head, tile_rp, tile_rp + tile_len, lo_rp, g_team);  // ends with a barrier
+      if (has_next) handoff_arrive(kBarInsert + (int)team);
+      LZ_PROF(kProfInsert);
+      if (g_team.tid == 0) *t_ctr = 0;
+      for (uint32_t i = (uint32_t)g_team.tid; i < (uint32_t)kTile / 32; i += kTeamThreads) t_deep[i] = 0;
+      group_sync(g_team);
       const long long t_ws = P.prof ? clock64() : 0;
-      search_tile(s_data, s_prev, s_mlen, s_mdist, tile_rp, tile_len, crp + chunk_len, lo_rp, &s_misc[kMRunCtr]);
-      if (P.prof && lane == 0) atomicAdd(&P.prof[kProfWarpSearch], (unsigned long long)(clock64() - t_ws) / 32);
-      __syncthreads();
+      search_tile(s_data, s_prev, t_mlen, t_mdist, tile_rp, tile_len, crp + chunk_len, lo_rp, t_ctr);
+      if (P.prof && team == 0 && lane == 0)
+        atomicAdd(&P.prof[kProfWarpSearch], (unsigned long long)(clock64() - t_ws) / kTeamWarps);
+      group_sync(g_team);
       LZ_PROF(kProfSearch);
-      // refine: parse, deep-search the token starts and their successors, repeat
-      for (uint32_t i = tid; i < (uint32_t)kTile / 32; i += kLzThreads) s_deep[i] = 0;
+      // -- stage B: the refine rounds parse from the tile start (the true first token start is not known before tile
+      // t-1 has been parsed for good; a parse from a wrong start joins the true one within a few tokens, and this
+      // way the choice of deep-searched positions does not depend on timing)
       for (int r = 0; r < kRefineRounds; r++) {
-        if (warp < (uint32_t)kParseWarps) parse_tile_wide(s_mlen, s_bitmap, (int)s_misc[kMStart], tile_len, 2);
-        if (tid == 0) s_misc[kMRunCtr] = 0;
-        __syncthreads();
+        if (g_team.tid < kParseThreads)
+          parse_tile_wide(t_mlen, t_bitmap, 0, tile_len, g_team.tid, kBarParse + (int)team);
+        if (g_team.tid == 0) *t_ctr = 0;
+        group_sync(g_team);
         LZ_PROF(kProfRefParse);
-        const uint32_t nwork = refine_build_list(s_mlen, s_mdist, s_bitmap, s_deep, s_work, s_misc + kMScan, tile_len);
+        const uint32_t nwork = refine_build_list(t_mlen, t_mdist, t_bitmap, t_deep, t_work, t_scan, tile_len, g_team);
         LZ_PROF(kProfRefList);
         const long long t_wd = P.prof ? clock64() : 0;
-        refine_search(s_data, s_prev, s_mlen, s_mdist, s_work, nwork, tile_rp, crp + chunk_len, lo_rp,
-                      &s_misc[kMRunCtr]);
-        if (P.prof && lane == 0) atomicAdd(&P.prof[kProfWarpDeep], (unsigned long long)(clock64() - t_wd) / 32);
-        __syncthreads();
+        refine_search(s_data, s_prev, t_mlen, t_mdist, t_work, nwork, tile_rp, crp + chunk_len, lo_rp, t_ctr);
+        if (P.prof && team == 0 && lane == 0)
+          atomicAdd(&P.prof[kProfWarpDeep], (unsigned long long)(clock64() - t_wd) / kTeamWarps);
+        group_sync(g_team);
         LZ_PROF(kProfRefDeep);
       }
-      // Warp 0 parses this tile (a latency-bound single-warp job) while the other 31 warps load and hash the next
-      if (warp < (uint32_t)kParseWarps) {
-        const int nxt = parse_tile_wide(s_mlen, s_bitmap, (int)s_misc[kMStart], tile_len, 2);
-        if (tid == 0) s_misc[kMStart] = (uint32_t)nxt;
-      } else if (t + 1 < ntiles) {
-        const int nrp = tile_rp + kTile;
-        const int nlen = chunk_len - (t + 1) * kTile < kTile ? chunk_len - (t + 1) * kTile : kTile;
-        load_ring(s_data, P, rs, nrp + kLook, nrp + kTile + kLook, g_rest);
-        group_sync(g_rest);
-        insert_positions(s_data, s_prev, s_head, nrp, nrp + nlen, lo_rp, g_rest);
-      }
-      __syncthreads();
+      // -- stage C: final parse and token emission, in tile order
+      if (t > 0) handoff_wait(kBarEmit + (int)(team ^ 1u));  // tile t-1 has emitted: kMStart and kMNTok are ours
+      LZ_PROF(kProfWaitB);
+      int nxt = 0;
+      if (g_team.tid < kParseThreads)
+        nxt = parse_tile_wide(t_mlen, t_bitmap, (int)s_misc[kMStart], tile_len, g_team.tid, kBarParse + (int)team);
+      group_sync(g_team);
       LZ_PROF(kProfParse);
       // emit tokens: rank of every start position, then token words + histograms
       {
-        const int t0 = (int)tid * kRun;
-        const uint32_t bits = (s_bitmap[t0 >> 5] >> (t0 & 31)) & ((1u << kRun) - 1u);
+        const int t0 = g_team.tid * kRun;
+        const uint32_t bits = (t_bitmap[t0 >> 5] >> (t0 & 31)) & ((1u << kRun) - 1u);
         uint32_t total;
-        uint32_t rank = block_exclusive_scan((uint32_t)__popc(bits), s_misc + kMScan, &total);
+        uint32_t rank = group_exclusive_scan((uint32_t)__popc(bits), t_scan, &total, g_team);
         const uint32_t base = s_misc[kMNTok];
         uint32_t m = bits;
         while (m) {
           const int j = __ffs((int)m) - 1;
           m &= m - 1;
           const int tp = t0 + j;
-          const uint32_t l = s_mlen[tp];
+          const uint32_t l = t_mlen[tp];
           uint32_t tok;
           // the lazy rule may have deferred a match: a start with a longer match right behind it is a literal
-          const bool lit = l == 0 || (tp + 1 < tile_len && s_mlen[tp + 1] > l);
+          const bool lit = l == 0 || (tp + 1 < tile_len && t_mlen[tp + 1] > l);
           if (lit) {
             tok = s_data[ring_slot(tile_rp + tp)];
             atomicAdd(&s_lfreq[tok], 1u);
           } else {
-            const uint32_t d = s_mdist[tp] & 0x7fffu;
+            const uint32_t d = t_mdist[tp] & 0x7fffu;
             tok = kTokMatch | (l << 16) | (d - 1);  // l = len-3
             atomicAdd(&s_lfreq[257 + len_code(l + 3)], 1u);
             atomicAdd(&s_dfreq[dist_code(d)], 1u);
           }
           tokens[base + rank++] = tok;
         }
-        __syncthreads();
-        if (tid == 0) s_misc[kMNTok] = base + total;
-        __syncthreads();
+        group_sync(g_team);  // everybody has read kMNTok and kMStart
+        if (g_team.tid == 0) {
+          s_misc[kMNTok] = base + total;
+          s_misc[kMStart] = (uint32_t)nxt;
+        }
+        if (has_next) handoff_arrive(kBarEmit + (int)team);
       }
       LZ_PROF(kProfEmit);
     }
+    __syncthreads();
+    LZ_PROF(kProfJoin);
 
     // ---- Huffman tables and exact sizes ------------------------------------------------------------------
     if (tid == 0) {

@@ -373,7 +373,7 @@ int lz_launch(dsg_ctx *ctx, cudaStream_t stream, const uint8_t *d_in, uint64_t l
     CU(cudaMemcpyAsync(h, P.prof, sizeof h, cudaMemcpyDeviceToHost, stream));
     CU(cudaStreamSynchronize(stream));
     static const char *names[kProfCount] = {"load", "insert", "search", "parse", "emit", "huffman", "sizes", "pack",
-                                              "ref_parse", "ref_list", "ref_deep"};
+                                              "ref_parse", "ref_list", "ref_deep", "wait_a", "wait_b", "join"};
     unsigned long long tot = 0;
     for (int i = 0; i < kProfCount; i++) tot += h[i];
     fprintf(stderr, "[lz prof] chunks=%u grid=%u cycles/chunk:", nchunks, grid);

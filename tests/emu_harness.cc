@@ -8,9 +8,6 @@
 
 #include <vector>
 
-#if defined(DSG_EMU_STATS)
-extern "C" { unsigned long long g_dsg_stat[16] = {0}; }
-#endif
 #include "crc32.cuh"
 #include "deflate_lz.cuh"
 #include "tar_kernels.cuh"

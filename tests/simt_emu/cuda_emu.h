@@ -188,6 +188,15 @@ inline void named_barrier_sync(int id, int count) {
   while (b->nb_gen[id] == my_gen) yield();
 }
 
+// bar.arrive id, count: counts the thread in without waiting
+inline void named_barrier_arrive(int id, int count) {
+  BlockState *b = cur_block();
+  if (++b->nb_arrived[id] >= (unsigned)count) {
+    b->nb_arrived[id] = 0;
+    b->nb_gen[id]++;
+  }
+}
+
 inline unsigned lane_id() { return (threadIdx.x + threadIdx.y * blockDim.x + threadIdx.z * blockDim.x * blockDim.y) & 31; }
 inline unsigned warp_id() { return (threadIdx.x + threadIdx.y * blockDim.x + threadIdx.z * blockDim.x * blockDim.y) >> 5; }
 
