@@ -44,10 +44,10 @@ namespace dsg {
 constexpr int kLzThreads = 1024;
 constexpr int kLzWarps = kLzThreads / 32;
 constexpr int kChunk = 65536;
-constexpr int kTeams = 2;                // the CTA works as two teams of 16 warps on alternate tiles (see the kernel)
+constexpr int kTeams = 4;                // the CTA works as two teams of 16 warps on alternate tiles (see the kernel)
 constexpr int kTeamThreads = kLzThreads / kTeams;
 constexpr int kTeamWarps = kTeamThreads / 32;
-constexpr int kTile = 4096;
+constexpr int kTile = 2048;
 constexpr int kDict = 32768;
 constexpr int kRing = kDict + kTeams * kTile;  // 40960 ring slots (bytes): the window + one tile per team
 constexpr int kLook = 272;               // look-ahead beyond a tile (>= 258 + 3, multiple of 16)
@@ -106,9 +106,10 @@ static_assert(kMaxDist % 16 == 0 && kLook % 16 == 0, "ring loads move 16-byte gr
 
 // misc[] slots
 enum { kMTicket = 0, kMStart, kMNTok, kMMode, kMOutLo, kMOutHi, kMHdrBits, kMChunkBytes, kMHlit, kMHdist, kMHclen,
-       kMNRle, kMBodyDyn, kMBodyFix, kMError, kMRunCtr /* one per team */, kMRunCtr1,
+       kMNRle, kMBodyDyn, kMBodyFix, kMError, kMRunCtr /* kTeams slots */,
        kMScan = 32 /* CTA scan: 32 warp partials + carry; team scans: 20 words each */, kMTeamScan = kMScan,
        kMTeamScanStride = 20 };
+static_assert(kMRunCtr + kTeams <= kMScan && kMTeamScan + kTeams * kMTeamScanStride <= 192, "misc[] slots");
 
 // Kernel parameter block
 struct LzParams {
@@ -131,8 +132,9 @@ enum { kProfLoad = 0, kProfInsert, kProfSearch, kProfParse, kProfEmit, kProfHuff
        kProfWarpSearch = kProfCount, kProfWarpDeep, kProfSlots };
 
 // named barriers: 0 = the CTA
-enum { kBarTeam = 1 /* +team */, kBarInsert = 3 /* +producing team */, kBarEmit = 5 /* +producing team */,
-       kBarParse = 7 /* +team */ };
+enum { kBarTeam = 1 /* +team */, kBarInsert = kBarTeam + kTeams /* +producing team */,
+       kBarEmit = kBarInsert + kTeams /* +producing team */, kBarEnd = kBarEmit + kTeams };
+static_assert(kBarEnd <= 16, "an SM has 16 named barriers");
 
 DSG_D uint32_t ring_slot(int rp /* run-relative position, >= -kDict */) {
   return (uint32_t)(rp + kDict) % (uint32_t)kRing;
@@ -157,21 +159,21 @@ DSG_D void group_sync(const LzGroup &g) {
   }
 }
 
-// Producer/consumer hand-off between the two teams on a named barrier: the producing team arrives (does not wait),
-// the consuming team waits; the barrier completes when all kLzThreads threads have done one or the other.
+// Producer/consumer hand-off between two teams on a named barrier: the producing team arrives (does not wait),
+// the consuming team waits; the barrier completes when the threads of both teams have done one or the other.
 DSG_D void handoff_arrive(int bar) {
   __threadfence_block();
 #if defined(DSG_EMU)
-  emu::named_barrier_arrive(bar, kLzThreads);
+  emu::named_barrier_arrive(bar, 2 * kTeamThreads);
 #else
-  asm volatile("bar.arrive %0, %1;" ::"r"(bar), "r"(kLzThreads) : "memory");
+  asm volatile("bar.arrive %0, %1;" ::"r"(bar), "r"(2 * kTeamThreads) : "memory");
 #endif
 }
 DSG_D void handoff_wait(int bar) {
 #if defined(DSG_EMU)
-  emu::named_barrier_sync(bar, kLzThreads);
+  emu::named_barrier_sync(bar, 2 * kTeamThreads);
 #else
-  asm volatile("bar.sync %0, %1;" ::"r"(bar), "r"(kLzThreads) : "memory");
+  asm volatile("bar.sync %0, %1;" ::"r"(bar), "r"(2 * kTeamThreads) : "memory");
 #endif
 }
 
@@ -702,8 +704,8 @@ DSG_D int parse_step(const uint8_t *s_mlen, int tp, int tile_len) {
 //      the entry its marks were made for re-walks until it meets a marked position (next() is stateless, so from
 //      there on the old marks and the old exit stand); repeated until no exit of the warp changes;
 //   3. the segment exits travel through shared memory the same way, until no segment exit changes.
-// Called by the first kParseThreads threads of a team (gtid = index inside the team); `bar` is a named barrier
-// for exactly those threads. Returns the first token start of the following tile, relative to that tile.
+// Called by all threads of a team (its first kParseThreads threads do the work; the synchronisation is the team's
+// barrier). Returns the first token start of the following tile, relative to that tile. Ends with a barrier.
 // ---------------------------------------------------------------------------------------------------------
 constexpr int kParseWarps = kTile / 1024;
 constexpr int kParseThreads = kParseWarps * 32;
@@ -757,42 +759,47 @@ DSG_D int parse_warp_settle(const uint8_t *s_mlen, uint32_t &cur, int &used, int
   return ex;
 }
 
-DSG_D int parse_tile_wide(const uint8_t *s_mlen, uint32_t *s_bitmap, int start, int tile_len, int gtid, int bar) {
-  const int g = gtid;  // 0 .. kParseThreads-1
+DSG_D int parse_tile_wide(const uint8_t *s_mlen, uint32_t *s_bitmap, int start, int tile_len, const LzGroup &team) {
+  const int g = team.tid;
+  const bool active = g < kParseThreads;  // the other threads of the team only keep the barriers company
   const int lane = g & 31, w = g >> 5;
   const int sub_lo = g * 32;
   const int sub_hi = sub_lo + 32 < tile_len ? sub_lo + 32 : tile_len;
   uint32_t *s_x = s_bitmap + kTile / 32;  // [0, kParseWarps): segment exits; [kParseWarps, +2): change flags
-  const LzGroup grp{g, kParseThreads, bar};
   uint32_t cur = 0;
   int seg_entry = w == 0 ? start : w * 1024;
   int used = lane == 0 ? seg_entry : sub_lo;
-  int ex = parse_lane_walk(s_mlen, cur, used, sub_lo, sub_hi, tile_len);
-  ex = parse_warp_settle(s_mlen, cur, used, ex, seg_entry, sub_lo, sub_hi, tile_len);
-  if (lane == 31) s_x[w] = (uint32_t)ex;
+  int ex = 0;
+  if (active) {
+    ex = parse_lane_walk(s_mlen, cur, used, sub_lo, sub_hi, tile_len);
+    ex = parse_warp_settle(s_mlen, cur, used, ex, seg_entry, sub_lo, sub_hi, tile_len);
+    if (lane == 31) s_x[w] = (uint32_t)ex;
+  }
   if (g == 0) {
     s_x[kParseWarps] = 0;
     s_x[kParseWarps + 1] = 0;
   }
   for (int round = 0; round < kParseWarps + 1; round++) {
     uint32_t *flag = s_x + kParseWarps + (round & 1);
-    group_sync(grp);  // exits and the cleared flag are visible
-    const int e = w == 0 ? start : (int)s_x[w - 1];
-    bool changed = false;
-    if (e != seg_entry) {
-      seg_entry = e;
-      const int old = ex;
-      ex = parse_warp_settle(s_mlen, cur, used, ex, seg_entry, sub_lo, sub_hi, tile_len);
-      changed = lane == 31 && ex != old;
+    group_sync(team);  // exits and the cleared flag are visible
+    if (active) {
+      const int e = w == 0 ? start : (int)s_x[w - 1];
+      bool changed = false;
+      if (e != seg_entry) {
+        seg_entry = e;
+        const int old = ex;
+        ex = parse_warp_settle(s_mlen, cur, used, ex, seg_entry, sub_lo, sub_hi, tile_len);
+        changed = lane == 31 && ex != old;
+      }
+      if (changed) *flag = 1u;
     }
-    if (changed) *flag = 1u;
-    group_sync(grp);  // every exit has been read, every flag written
-    if (lane == 31) s_x[w] = (uint32_t)ex;
+    group_sync(team);  // every exit has been read, every flag written
+    if (active && lane == 31) s_x[w] = (uint32_t)ex;
     if (g == 0) s_x[kParseWarps + ((round + 1) & 1)] = 0;
     if (*flag == 0u) break;
   }
-  s_bitmap[g] = cur;
-  group_sync(grp);
+  if (active) s_bitmap[g] = cur;
+  group_sync(team);
   return (int)s_x[kParseWarps - 1] - tile_len;  // >= 0: first token start of the following tile, relative to it
 }
 
@@ -935,6 +942,7 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   // the team's private arrays
   const uint32_t team = warp / kTeamWarps;
+  const uint32_t prev_team = (team + kTeams - 1) % kTeams;  // owns the tile before each of ours
   const LzGroup g_team{(int)(tid - team * kTeamThreads), kTeamThreads, kBarTeam + (int)team};
   uint8_t *t_mlen = s_mlen + team * kTile;
   uint16_t *t_mdist = s_mdist + team * kTile;
@@ -1005,7 +1013,7 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
       const int tile_len = chunk_len - t * kTile < kTile ? chunk_len - t * kTile : kTile;
       const bool has_next = t + 1 < ntiles;
       // -- stage A
-      if (t > 0) handoff_wait(kBarInsert + (int)(team ^ 1u));  // tile t-1 is in the chains
+      if (t > 0) handoff_wait(kBarInsert + (int)prev_team);  // tile t-1 is in the chains
       LZ_PROF(kProfWaitA);
       if (tile_rp > 0) {  // (the first tile of a run came with the dictionary) its bytes + look-ahead replace the oldest
         load_ring(s_data, P, rs, tile_rp + kLook, tile_rp + kTile + kLook, g_team);
@@ -1028,8 +1036,7 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
       // t-1 has been parsed for good; a parse from a wrong start joins the true one within a few tokens, and this
       // way the choice of deep-searched positions does not depend on timing)
       for (int r = 0; r < kRefineRounds; r++) {
-        if (g_team.tid < kParseThreads)
-          parse_tile_wide(t_mlen, t_bitmap, 0, tile_len, g_team.tid, kBarParse + (int)team);
+        parse_tile_wide(t_mlen, t_bitmap, 0, tile_len, g_team);
         if (g_team.tid == 0) *t_ctr = 0;
         group_sync(g_team);
         LZ_PROF(kProfRefParse);
@@ -1043,12 +1050,9 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
         LZ_PROF(kProfRefDeep);
       }
       // -- stage C: final parse and token emission, in tile order
-      if (t > 0) handoff_wait(kBarEmit + (int)(team ^ 1u));  // tile t-1 has emitted: kMStart and kMNTok are ours
+      if (t > 0) handoff_wait(kBarEmit + (int)prev_team);  // tile t-1 has emitted: kMStart and kMNTok are ours
       LZ_PROF(kProfWaitB);
-      int nxt = 0;
-      if (g_team.tid < kParseThreads)
-        nxt = parse_tile_wide(t_mlen, t_bitmap, (int)s_misc[kMStart], tile_len, g_team.tid, kBarParse + (int)team);
-      group_sync(g_team);
+      const int nxt = parse_tile_wide(t_mlen, t_bitmap, (int)s_misc[kMStart], tile_len, g_team);
       LZ_PROF(kProfParse);
       // emit tokens: rank of every start position, then token words + histograms
       {

@@ -17,6 +17,7 @@
 
 #include "crc32.cuh"
 #include "deflate_lz.cuh"
+#include "file_crc.cuh"
 #include "deflate_stored.cuh"
 #include "tar_kernels.cuh"
 
@@ -76,6 +77,8 @@ struct dsg_ctx {
   DevBuf d_entries, d_strtab, d_arena, d_tar, d_out;
   // crc
   DevBuf crc_raw;
+  // per-file crc (context hash)
+  DevBuf fc_files, fc_units, fc_first, fc_totals, fc_raw, fc_crcs;
   // deflate
   DevBuf lz_scratch, chunk_sizes, chunk_slots, chunk_offs, lz_prof;
   // pipelined path: two slots each for the arena slice, the tar segment and the compressed segment
@@ -494,6 +497,7 @@ void dsg_ctx_destroy(dsg_ctx *ctx) {
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   for (DevBuf *b : {&ctx->crc_tab, &ctx->crc_shift, &ctx->ent_blocks, &ctx->cta_sums, &ctx->ent_off, &ctx->scalars,
                     &ctx->d_entries, &ctx->d_strtab, &ctx->d_arena, &ctx->d_tar, &ctx->d_out, &ctx->crc_raw,
+                    &ctx->fc_files, &ctx->fc_units, &ctx->fc_first, &ctx->fc_totals, &ctx->fc_raw, &ctx->fc_crcs,
                     &ctx->lz_scratch, &ctx->chunk_sizes, &ctx->chunk_slots, &ctx->chunk_offs, &ctx->lz_prof, &ctx->seg_ranges, &ctx->slot_arena[0],
                     &ctx->slot_arena[1], &ctx->slot_tar[0], &ctx->slot_tar[1], &ctx->slot_out[0], &ctx->slot_out[1]})
     b->release();
@@ -648,6 +652,104 @@ int dsg_dev_crc32(dsg_ctx *ctx, const uint8_t *d_buf, size_t len, uint32_t *crc)
   *crc = (uint32_t)ctx->h_scalars[kSCrc];
   ctx->stats.ms_crc = elapsed(ctx, kTimCrc);
   ctx->stats.crc32 = *crc;
+  ctx->stats.kernel_launches = ctx->launches;
+  return DSG_OK;
+}
+
+// ---- per-file CRC32 (build-context hash, pkg/util/hash/hash.go:165-197) ----------------------------------------
+
+namespace {
+// d_crcs[i] = CRC32-IEEE of entry i's payload (0 for directories and empty files). Asynchronous on ctx->stream
+// except for one synchronisation that reads the number of units.
+int file_crc_run(dsg_ctx *ctx, const dsg_entry *d_entries, uint32_t n, const uint8_t *d_arena, uint64_t arena_len,
+                 uint32_t *d_crcs) {
+  if (n == 0) return DSG_OK;
+  cudaStream_t st = ctx->stream;
+  const uint32_t nblk = (n + kScanBlock - 1) / kScanBlock;
+  CU(ctx->fc_files.ensure(sizeof(FileCrcEntry) * (size_t)n));
+  CU(ctx->fc_units.ensure(sizeof(uint32_t) * (size_t)n));
+  CU(ctx->fc_first.ensure(sizeof(uint32_t) * ((size_t)n + 1)));
+  CU(ctx->fc_totals.ensure(sizeof(uint32_t) * ((size_t)nblk + 2)));
+  FileCrcEntry *files = ctx->fc_files.as<FileCrcEntry>();
+  uint32_t *units = ctx->fc_units.as<uint32_t>(), *first = ctx->fc_first.as<uint32_t>();
+  uint32_t *totals = ctx->fc_totals.as<uint32_t>();
+  uint32_t *grand = totals + nblk, *error = totals + nblk + 1;
+  CU(cudaMemsetAsync(error, 0, sizeof(uint32_t), st));
+  fcrc_extract_kernel<<<(n + 255) / 256, 256, 0, st>>>(reinterpret_cast<const uint8_t *>(d_entries), n,
+                                                      (uint32_t)sizeof(dsg_entry), (uint32_t)offsetof(dsg_entry, size),
+                                                      (uint32_t)offsetof(dsg_entry, data_off),
+                                                      (uint32_t)offsetof(dsg_entry, typeflag), arena_len, files, error);
+  LAUNCH_CHECK();
+  fcrc_count_kernel<<<(n + 255) / 256, 256, 0, st>>>(files, n, (uint64_t)(uintptr_t)d_arena, units);
+  LAUNCH_CHECK();
+  fcrc_scan_blocks_kernel<<<nblk, kScanBlock, 0, st>>>(units, n, first, totals);
+  LAUNCH_CHECK();
+  fcrc_scan_totals_kernel<<<1, kScanBlock, 0, st>>>(totals, nblk, grand);
+  LAUNCH_CHECK();
+  fcrc_scan_add_kernel<<<nblk, kScanBlock, 0, st>>>(first, n, totals, grand);
+  LAUNCH_CHECK();
+  uint32_t h[2] = {0, 0};  // grand total, error
+  CU(cudaMemcpyAsync(h, grand, sizeof h, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  if (h[1]) return fail(ctx, DSG_E_RANGE, "entry %u: payload range outside the arena", h[1] - 1);
+  const uint32_t nunits = h[0];
+  CU(ctx->fc_raw.ensure(sizeof(uint32_t) * ((size_t)nunits + 1)));
+  if (nunits) {
+    fcrc_units_kernel<<<nunits, kCrcThreads, 0, st>>>(files, n, d_arena, first, ctx->crc_tab.as<uint32_t>(),
+                                                       ctx->crc_shift.as<uint32_t>(), ctx->fc_raw.as<uint32_t>());
+    LAUNCH_CHECK();
+  }
+  fcrc_join_kernel<<<(n + 7) / 8, 256, 0, st>>>(files, n, d_arena, first, ctx->fc_raw.as<uint32_t>(), d_crcs);
+  LAUNCH_CHECK();
+  return DSG_OK;
+}
+}  // namespace
+
+extern "C" int dsg_dev_file_crc32(dsg_ctx *ctx, const dsg_entry *d_entries, size_t n, const uint8_t *d_arena,
+                                  size_t arena_len, uint32_t *d_crcs) {
+  if (!ctx || (n && (!d_entries || !d_crcs)) || (arena_len && !d_arena) || n > 0x7fffffffu) return DSG_E_ARG;
+  std::lock_guard<std::mutex> g(ctx->mu);
+  int rc = begin_call(ctx);
+  if (rc) return rc;
+  tic(ctx, kTimCrc);
+  if ((rc = file_crc_run(ctx, d_entries, (uint32_t)n, d_arena, arena_len, d_crcs))) return rc;
+  toc(ctx, kTimCrc);
+  CU(cudaStreamSynchronize(ctx->stream));
+  ctx->stats.entries = n;
+  ctx->stats.ms_crc = elapsed(ctx, kTimCrc);
+  ctx->stats.ms_total = ctx->stats.ms_crc;
+  ctx->stats.kernel_launches = ctx->launches;
+  return DSG_OK;
+}
+
+extern "C" int dsg_file_crc32(dsg_ctx *ctx, const dsg_entry *entries, size_t n, const uint8_t *arena, size_t arena_len,
+                              uint32_t *crcs) {
+  if (!ctx || (n && (!entries || !crcs)) || (arena_len && !arena) || n > 0x7fffffffu) return DSG_E_ARG;
+  std::lock_guard<std::mutex> g(ctx->mu);
+  int rc = begin_call(ctx);
+  if (rc) return rc;
+  if (n == 0) return DSG_OK;
+  CU(ctx->d_entries.ensure(sizeof(dsg_entry) * n));
+  CU(ctx->d_arena.ensure(arena_len + 16));
+  CU(ctx->fc_crcs.ensure(sizeof(uint32_t) * n));
+  Timer &tt = ctx->tim[kTimTotal];
+  cudaEventRecord(tt.a, ctx->stream);
+  CU(cudaMemcpyAsync(ctx->d_entries.p, entries, sizeof(dsg_entry) * n, cudaMemcpyHostToDevice, ctx->stream));
+  if (arena_len) CU(cudaMemcpyAsync(ctx->d_arena.p, arena, arena_len, cudaMemcpyHostToDevice, ctx->stream));
+  tic(ctx, kTimCrc);
+  if ((rc = file_crc_run(ctx, ctx->d_entries.as<dsg_entry>(), (uint32_t)n, ctx->d_arena.as<uint8_t>(), arena_len,
+                         ctx->fc_crcs.as<uint32_t>())))
+    return rc;
+  toc(ctx, kTimCrc);
+  CU(cudaMemcpyAsync(crcs, ctx->fc_crcs.p, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost, ctx->stream));
+  cudaEventRecord(tt.b, ctx->stream);
+  tt.used = true;
+  CU(cudaStreamSynchronize(ctx->stream));
+  ctx->stats.entries = n;
+  ctx->stats.h2d_bytes = sizeof(dsg_entry) * n + arena_len;
+  ctx->stats.d2h_bytes = sizeof(uint32_t) * n;
+  ctx->stats.ms_crc = elapsed(ctx, kTimCrc);
+  ctx->stats.ms_total = elapsed(ctx, kTimTotal);
   ctx->stats.kernel_launches = ctx->launches;
   return DSG_OK;
 }

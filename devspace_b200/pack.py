@@ -180,6 +180,20 @@ class Packer:
         self._check(self._lib.dsg_dev_crc32(self._ctx, c_void_p(d_buf.ptr + offset), nbytes, byref(crc)))
         return crc.value
 
+    def file_crc32_device(self, dm: "DeviceManifest", d_crcs: DeviceBuffer) -> None:
+        """hashFileCRC32 (pkg/util/hash/hash.go:165) of every entry of a resident manifest, into d_crcs (u32[n])."""
+        self._check(self._lib.dsg_dev_file_crc32(self._ctx, dm.entries.ptr, dm.n, dm.arena.ptr, dm.arena_len,
+                                                 d_crcs.ptr))
+
+    def file_crc32(self, man: Manifest) -> np.ndarray:
+        """Per-file CRC32-IEEE of a host manifest (one host->device pass of the arena)."""
+        crcs = np.zeros(max(1, man.n), np.uint32)
+        ent = np.ascontiguousarray(man.entries)
+        arena = np.ascontiguousarray(man.arena)
+        self._check(self._lib.dsg_file_crc32(self._ctx, c_void_p(ent.ctypes.data), man.n,
+                                             c_void_p(arena.ctypes.data), int(arena.size), c_void_p(crcs.ctypes.data)))
+        return crcs[:man.n]
+
     def deflate_device(self, d_in: DeviceBuffer, nbytes: int, d_out: DeviceBuffer, level: Optional[int] = None) -> int:
         n = c_size_t()
         lvl = self.level if level is None else level

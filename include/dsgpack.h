@@ -222,6 +222,19 @@ int dsg_dev_tar_build(dsg_ctx *ctx, const dsg_entry *d_entries, size_t n, const 
 /* hash/crc32 ChecksumIEEE over d_buf[0,len) (gzip.Writer keeps it as z.digest). */
 int dsg_dev_crc32(dsg_ctx *ctx, const uint8_t *d_buf, size_t len, uint32_t *crc);
 
+/* Build-context hash, per-file part: hashFileCRC32, pkg/util/hash/hash.go:165-197
+ * (crc32.New(crc32.MakeTable(0xedb88320)) over the file's bytes), which DirectoryExcludes calls for every context
+ * file (hash.go:146) before each build decision (pkg/devspace/image/build.go:213). crcs[i] = CRC32-IEEE of entry
+ * i's payload arena[data_off, data_off+size); 0 for directories and empty files (Go: the checksum of no bytes).
+ * The manifest and arena are the ones dsg_pack / dsg_pack_device take, so an arena that is resident for packing
+ * yields the checksums without another host->device pass. dsg_file_crc32: host buffers in, host array out
+ * (arena ideally pinned); dsg_dev_file_crc32: everything device resident. DSG_E_RANGE when a payload range lies
+ * outside the arena. The SHA-256 over the short "path;crc" list stays on the host (dsg_directory_hash below). */
+int dsg_file_crc32(dsg_ctx *ctx, const dsg_entry *entries, size_t n, const uint8_t *arena, size_t arena_len,
+                   uint32_t *crcs);
+int dsg_dev_file_crc32(dsg_ctx *ctx, const dsg_entry *d_entries, size_t n, const uint8_t *d_arena, size_t arena_len,
+                       uint32_t *d_crcs);
+
 /* compress/flate Writer at `level`: raw deflate stream (byte aligned, BFINAL set on the last block)
  * of d_in[0,len) into d_out[out_cap]. */
 int dsg_dev_deflate(dsg_ctx *ctx, const uint8_t *d_in, size_t len, int level, uint8_t *d_out, size_t out_cap,
@@ -247,6 +260,18 @@ void *dsg_dev_alloc(dsg_ctx *ctx, size_t bytes);
 void dsg_dev_free(dsg_ctx *ctx, void *d_ptr);
 int dsg_dev_upload(dsg_ctx *ctx, void *d_dst, const void *src, size_t bytes);
 int dsg_dev_download(dsg_ctx *ctx, void *dst, const void *d_src, size_t bytes);
+
+/* ---- Build-context hash, host side -------------------------------------------------------
+ * DirectoryExcludes(srcPath, excludePatterns), pkg/util/hash/hash.go:43-163: filepath.Walk order, the exclude
+ * decisions, "filePath" for a directory and "filePath;crc32hex" for a file into SHA-256, lower-case hex out.
+ * The pattern matcher of the reference (docker/pkg/fileutils) stays with the caller: `exclude` gets the relative
+ * path as hash.go builds it ("./a/b") and returns 0 = keep, 1 = skip (a directory is not entered, hash.go:120,134),
+ * 2 = leave this entry out but enter the directory (an exclusion pattern "!dir/x" lies below it, hash.go:122-131).
+ * NULL keeps everything. File bytes are read into one pinned arena and checksummed by dsg_file_crc32 on the GPU.
+ * out_hex: 64 hex digits + NUL. err/err_len: optional buffer for the error text. */
+typedef int (*dsg_exclude_fn)(const char *rel_path, int is_dir, void *user);
+int dsg_directory_hash(dsg_ctx *ctx, const char *src_path, dsg_exclude_fn exclude, void *user, char out_hex[65],
+                       char *err, size_t err_len);
 
 #ifdef __cplusplus
 }

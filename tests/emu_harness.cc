@@ -10,6 +10,7 @@
 
 #include "crc32.cuh"
 #include "deflate_lz.cuh"
+#include "file_crc.cuh"
 #include "tar_kernels.cuh"
 
 dim3 threadIdx, blockIdx, blockDim, gridDim;
@@ -118,6 +119,37 @@ uint32_t emu_crc32(const uint8_t *buf, uint64_t len) {
   emu::launch(dim3(1), dim3(256), 0,
               [&] { crc_join_kernel(raw.data(), ntiles, body, buf, head, buf + head + body, tail, state); });
   return state[0];
+}
+
+// Mirrors file_crc_run in dsgpack.cu: entries = n records of `stride` bytes (dsg_entry layout offsets passed in).
+int emu_file_crc32(const uint8_t *entries, uint32_t n, uint32_t stride, uint32_t off_size, uint32_t off_data,
+                   uint32_t off_type, const uint8_t *arena, uint64_t arena_len, uint32_t *crcs) {
+  if (n == 0) return 0;
+  std::vector<uint32_t> tab(kCrcTables * 256), shift(kCrcShiftEntries);
+  crc_build_tables(tab.data(), shift.data(), (uint64_t)kCrcThreads * 16);
+  const uint32_t nblk = (n + kScanBlock - 1) / kScanBlock;
+  std::vector<FileCrcEntry> files(n);
+  std::vector<uint32_t> units(n), first(n + 1), totals(nblk + 2, 0);
+  uint32_t *grand = totals.data() + nblk, *error = totals.data() + nblk + 1;
+  emu::launch(dim3((n + 255) / 256), dim3(256), 0, [&] {
+    fcrc_extract_kernel(entries, n, stride, off_size, off_data, off_type, arena_len, files.data(), error);
+  });
+  emu::launch(dim3((n + 255) / 256), dim3(256), 0,
+              [&] { fcrc_count_kernel(files.data(), n, (uint64_t)(uintptr_t)arena, units.data()); });
+  emu::launch(dim3(nblk), dim3(kScanBlock), 0,
+              [&] { fcrc_scan_blocks_kernel(units.data(), n, first.data(), totals.data()); });
+  emu::launch(dim3(1), dim3(kScanBlock), 0, [&] { fcrc_scan_totals_kernel(totals.data(), nblk, grand); });
+  emu::launch(dim3(nblk), dim3(kScanBlock), 0, [&] { fcrc_scan_add_kernel(first.data(), n, totals.data(), grand); });
+  if (*error) return -(int)*error;
+  const uint32_t nunits = *grand;
+  std::vector<uint32_t> raw(nunits + 1);
+  if (nunits)
+    emu::launch(dim3(nunits), dim3(kCrcThreads), 0, [&] {
+      fcrc_units_kernel(files.data(), n, arena, first.data(), tab.data(), shift.data(), raw.data());
+    });
+  emu::launch(dim3((n + 7) / 8), dim3(256), 0,
+              [&] { fcrc_join_kernel(files.data(), n, arena, first.data(), raw.data(), crcs); });
+  return 0;
 }
 
 }  // extern "C"
