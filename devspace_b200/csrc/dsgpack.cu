@@ -414,7 +414,7 @@ const char *dsg_strerror(int status) {
     case DSG_E_ARG: return "invalid argument";
     case DSG_E_CUDA: return "CUDA error";
     case DSG_E_HEADER: return "archive/tar: header field cannot be encoded";
-    case DSG_E_TYPEFLAG: return "typeflag is neither '0' nor '5'";
+    case DSG_E_TYPEFLAG: return "typeflag is none of '0' (file), '5' (directory), '1' (hard link), '2' (symlink)";
     case DSG_E_CAPACITY: return "output buffer too small";
     case DSG_E_UNCLEAN_NAME: return "PAX entry name is not path.Clean()ed";
     case DSG_E_NOMEM: return "out of device or pinned memory";

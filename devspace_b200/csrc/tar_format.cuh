@@ -24,7 +24,14 @@ enum : uint32_t {
   kPaxGid = 32u,
   kPaxSize = 64u,
   kPaxMtime = 128u,
+  kPaxLinkpath = 256u,
 };
+
+// Link entries (typeflag '1' hard link, '2' symbolic link; docker's build-context dialect, not tar.go) carry no
+// payload: their data_off field holds the link target instead, as a strtab reference.
+DSG_HD bool is_link(const dsg_entry &e) { return e.typeflag == '1' || e.typeflag == '2'; }
+DSG_HD uint32_t link_off(const dsg_entry &e) { return (uint32_t)e.data_off; }
+DSG_HD uint32_t link_len(const dsg_entry &e) { return (uint32_t)(e.data_off >> 32); }
 
 struct HdrPlan {
   int64_t mtime;        // ModTime.Round(time.Second).Unix()
@@ -113,8 +120,10 @@ DSG_HD uint32_t split_ustar_path(const char *name, uint32_t len, bool ascii) {
   return (uint32_t)plen;
 }
 
-// Header.allowedFormats, restricted to the fields tar.go fills (no Linkname / Dev* / Xattrs /
-// PAXRecords; AccessTime and ChangeTime are cleared by WriteHeader because Format is unset).
+// Header.allowedFormats, restricted to the fields tar.go and docker's pkg/archive fill (no Dev* / Xattrs /
+// PAXRecords; AccessTime and ChangeTime are zero: cleared by WriteHeader when Format is unset, by docker's
+// FileInfoHeader otherwise). Format = FormatPAX (docker) decides nothing here: "PAX implies USTAR allowed too"
+// (allowedFormats), so USTAR is still written whenever it can hold the header.
 // Returns a dsg_status.
 DSG_HD int classify_entry(const dsg_entry &e, const char *strtab, uint64_t strtab_len, HdrPlan &p) {
   p.mtime = 0;
@@ -122,7 +131,8 @@ DSG_HD int classify_entry(const dsg_entry &e, const char *strtab, uint64_t strta
   p.rec_bytes = 0;
   p.flags = 0;
   p.prefix_len = 0;
-  if (e.typeflag != '0' && e.typeflag != '5') return DSG_E_TYPEFLAG;
+  if (e.typeflag != '0' && e.typeflag != '5' && !is_link(e)) return DSG_E_TYPEFLAG;
+  if (is_link(e) && (uint64_t)link_off(e) + link_len(e) > strtab_len) return DSG_E_ARG;
   if ((uint64_t)e.name_off + e.name_len > strtab_len || (uint64_t)e.uname_off + e.uname_len > strtab_len ||
       (uint64_t)e.gname_off + e.gname_len > strtab_len || e.mtime_nsec > 999999999u)
     return DSG_E_ARG;
@@ -140,6 +150,12 @@ DSG_HD int classify_entry(const dsg_entry &e, const char *strtab, uint64_t strta
     if (!pl) ustar_ok = false;
     p.prefix_len = pl;
     flags |= kPaxPath;
+  }
+  const char *lname = is_link(e) ? strtab + link_off(e) : name;
+  const uint32_t llen = is_link(e) ? link_len(e) : 0;
+  if (!is_ascii(lname, llen) || llen > (uint32_t)kNameSize) {  // verifyString(h.Linkname, paxLinkpath): no split
+    ustar_ok = false;
+    flags |= kPaxLinkpath;
   }
   if (!is_ascii(uname, e.uname_len) || e.uname_len > 32) {  // verifyString(h.Uname, paxUname)
     ustar_ok = false;
@@ -170,10 +186,10 @@ DSG_HD int classify_entry(const dsg_entry &e, const char *strtab, uint64_t strta
   }
   if (e.typeflag == '0' && e.name_len > 0 && name[e.name_len - 1] == '/') return DSG_E_HEADER;
   if (e.size < 0) return DSG_E_HEADER;
-  if (e.typeflag == '5' && e.size != 0) return DSG_E_HEADER;
+  if ((e.typeflag == '5' || is_link(e)) && e.size != 0) return DSG_E_HEADER;
   // validPAXRecord: no NUL inside path / uname / gname values
   if (((flags & kPaxPath) && has_nul(name, e.name_len)) || ((flags & kPaxUname) && has_nul(uname, e.uname_len)) ||
-      ((flags & kPaxGname) && has_nul(gname, e.gname_len)))
+      ((flags & kPaxGname) && has_nul(gname, e.gname_len)) || ((flags & kPaxLinkpath) && has_nul(lname, llen)))
     pax_ok = false;
   if (ustar_ok) {
     p.flags = 0;
@@ -183,9 +199,10 @@ DSG_HD int classify_entry(const dsg_entry &e, const char *strtab, uint64_t strta
   if (!pax_ok) return DSG_E_HEADER;
   p.prefix_len = 0;
   p.flags = flags | kNeedPax;
-  uint32_t rec = 0;  // sorted keys: gid gname mtime path size uid uname
+  uint32_t rec = 0;  // sorted keys: gid gname linkpath mtime path size uid uname
   if (flags & kPaxGid) rec += pax_record_len(3, (uint32_t)dec_len_i64(e.gid), nullptr);
   if (flags & kPaxGname) rec += pax_record_len(5, e.gname_len, nullptr);
+  if (flags & kPaxLinkpath) rec += pax_record_len(8, llen, nullptr);
   if (flags & kPaxMtime) rec += pax_record_len(5, (uint32_t)dec_len_i64(p.mtime), nullptr);
   if (flags & kPaxPath) rec += pax_record_len(4, e.name_len, nullptr);
   if (flags & kPaxSize) rec += pax_record_len(4, (uint32_t)dec_len_i64(e.size), nullptr);
@@ -270,6 +287,10 @@ DSG_HD void format_main_header(uint8_t *blk, const dsg_entry &e, const char *str
   const char *gname = strtab + e.gname_off;
   const bool pax = (p.flags & kNeedPax) != 0;
   blk[156] = e.typeflag;
+  if (is_link(e)) {
+    if (pax) format_string_to_ascii(blk + 157, 100, strtab + link_off(e), link_len(e));
+    else format_string(blk + 157, 100, strtab + link_off(e), link_len(e));
+  }
   if (pax) {
     format_string_to_ascii(blk, 100, name, e.name_len);
     format_string_to_ascii(blk + 265, 32, uname, e.uname_len);
@@ -296,10 +317,15 @@ DSG_HD void format_main_header(uint8_t *blk, const dsg_entry &e, const char *str
 }
 
 // True when path.Clean(name) == name can be relied on for building the PaxHeaders.0 name without
-// running Clean (names produced by tar.go always are: path.Join at tar.go:186,261).
-DSG_HD bool name_is_clean_for_pax(const char *s, uint32_t n) {
+// running Clean (names produced by tar.go always are: path.Join at tar.go:186,261). A directory may end in one
+// '/' (docker's canonicalTarName): path.Split then yields an empty file part and Join drops the slash again.
+DSG_HD bool name_is_clean_for_pax(const char *s, uint32_t n, bool dir_slash) {
   if (n == 0) return false;
-  if (n > 1 && s[n - 1] == '/') return false;
+  if (n > 1 && s[n - 1] == '/') {
+    if (!dir_slash) return false;
+    n--;
+    if (n > 1 && s[n - 1] == '/') return false;
+  }
   uint32_t i = 0;
   while (i < n) {
     if (s[i] == '/') {
@@ -323,7 +349,7 @@ DSG_HD bool name_is_clean_for_pax(const char *s, uint32_t n) {
 DSG_HD int format_pax_headers(uint8_t *dst, uint32_t win_lo, uint32_t win_hi, const dsg_entry &e,
                               const char *strtab, const HdrPlan &p) {
   const char *name = strtab + e.name_off;
-  if (!name_is_clean_for_pax(name, e.name_len)) return DSG_E_UNCLEAN_NAME;
+  if (!name_is_clean_for_pax(name, e.name_len, e.typeflag == '5')) return DSG_E_UNCLEAN_NAME;
   if (win_hi > p.hdr_bytes) win_hi = p.hdr_bytes;
   uint8_t tmp[kBlock];
   auto emit_block = [&](uint32_t at) {
@@ -375,6 +401,7 @@ DSG_HD int format_pax_headers(uint8_t *dst, uint32_t win_lo, uint32_t win_hi, co
   uint32_t nl;
   if (p.flags & kPaxGid) { nl = (uint32_t)dec_write_i64(e.gid, num); put("gid", 3, num, nl); }
   if (p.flags & kPaxGname) put("gname", 5, strtab + e.gname_off, e.gname_len);
+  if (p.flags & kPaxLinkpath) put("linkpath", 8, strtab + link_off(e), link_len(e));
   if (p.flags & kPaxMtime) { nl = (uint32_t)dec_write_i64(p.mtime, num); put("mtime", 5, num, nl); }
   if (p.flags & kPaxPath) put("path", 4, name, e.name_len);
   if (p.flags & kPaxSize) { nl = (uint32_t)dec_write_i64(e.size, num); put("size", 4, num, nl); }

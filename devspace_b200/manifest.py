@@ -36,6 +36,8 @@ assert ENTRY_DTYPE.itemsize == 80
 
 TYPE_REG = ord("0")
 TYPE_DIR = ord("5")
+TYPE_LINK = ord("1")      # hard link   } docker build-context dialect only: no payload, the target
+TYPE_SYMLINK = ord("2")   # symbolic link }   is a strtab reference in data_off (offset | length << 32)
 ARENA_ALIGN = 16  # payload starts are 16-byte aligned so the layout kernel moves 128-bit words
 
 
@@ -100,9 +102,12 @@ class ManifestBuilder:
         return off
 
     def add(self, name, size: int = 0, mtime_sec: int = 0, mtime_nsec: int = 0, mode: int = 0o644, uid: int = 0,
-            gid: int = 0, uname=b"", gname=b"", typeflag: int = TYPE_REG, data=None) -> None:
+            gid: int = 0, uname=b"", gname=b"", typeflag: int = TYPE_REG, data=None, linkname=b"") -> None:
         name, uname, gname = _b(name), _b(uname), _b(gname)
         data_off = 0
+        if typeflag in (TYPE_LINK, TYPE_SYMLINK):  # the link target travels in data_off as a strtab reference
+            linkname = _b(linkname)
+            data_off = self._name(linkname) | (len(linkname) << 32)
         if typeflag == TYPE_REG and size > 0:
             pad = (-self._arena_len) % self._align
             if pad:
@@ -120,7 +125,7 @@ class ManifestBuilder:
     def add_entry(self, e) -> None:
         """Accepts any object with the oracle.Entry attribute names (duck typed; no import of oracle)."""
         self.add(e.name, e.size, e.mtime_sec, e.mtime_nsec, e.mode, e.uid, e.gid, e.uname, e.gname, e.typeflag,
-                 e.data if e.typeflag == TYPE_REG and e.size > 0 else None)
+                 e.data if e.typeflag == TYPE_REG and e.size > 0 else None, getattr(e, "linkname", b""))
 
     def build(self) -> Manifest:
         ent = np.zeros(len(self._rows), ENTRY_DTYPE)

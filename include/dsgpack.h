@@ -50,7 +50,8 @@ typedef enum dsg_status {
  * Strings live in a caller-provided string table (`strtab`); several entries may share one string.
  */
 typedef struct dsg_entry {
-  uint64_t data_off;   /* payload offset in the arena (bytes); ignored when size == 0 or typeflag '5' */
+  uint64_t data_off;   /* payload offset in the arena (bytes); ignored when size == 0 or typeflag '5'.
+                        * typeflag '1' / '2': hdr.Linkname instead, as strtab offset | (length << 32)  */
   int64_t size;        /* hdr.Size: stat.Size() for files, 0 for directories                         */
   int64_t mtime_sec;   /* stat.ModTime() seconds; rounding to the nearest second (WriteHeader,        */
   int64_t mode;        /*   Format unset) is done on the device. mode: perm|04000|02000|01000         */
@@ -63,7 +64,7 @@ typedef struct dsg_entry {
   uint32_t gname_off;  /* hdr.Gname                                                                   */
   uint16_t uname_len;
   uint16_t gname_len;
-  uint8_t typeflag;    /* '0' regular file, '5' empty directory                                       */
+  uint8_t typeflag;    /* '0' regular file, '5' directory; '1' hard link, '2' symlink (docker dialect) */
   uint8_t reserved[7]; /* must be zero                                                                */
 } dsg_entry;
 
@@ -272,6 +273,17 @@ int dsg_dev_download(dsg_ctx *ctx, void *dst, const void *d_src, size_t bytes);
 typedef int (*dsg_exclude_fn)(const char *rel_path, int is_dir, void *user);
 int dsg_directory_hash(dsg_ctx *ctx, const char *src_path, dsg_exclude_fn exclude, void *user, char out_hex[65],
                        char *err, size_t err_len);
+
+/* ---- Docker build-context tar, host side -------------------------------------------------
+ * archive.TarWithOptions(contextDir, {ExcludePatterns, ChownOpts{0,0}}) as pkg/devspace/builder/docker/docker.go:94-97
+ * calls it (github.com/docker/docker/pkg/archive, go.mod:22; not under /root/reference: restated, parity unpinned):
+ * filepath.Walk order, no entry for the context directory itself, every directory an entry named "dir/", symlinks
+ * ('2') and further names of a multiply linked inode ('1') as link entries, mode with the file-type bits, mtime
+ * truncated to seconds, uid = gid = 0 with the owner's names kept, no compression. `exclude` as for
+ * dsg_directory_hash, except that rel_path is "a/b" (TarWithOptions does not prefix "./"). Device nodes, FIFOs and
+ * sockets are left out. The stream (what the reference pipes to the daemon) is written to out_path. */
+int dsg_docker_context_tar(dsg_ctx *ctx, const char *src_path, dsg_exclude_fn exclude, void *user, const char *out_path,
+                           uint64_t *tar_bytes, uint64_t *n_entries, char *err, size_t err_len);
 
 #ifdef __cplusplus
 }

@@ -50,6 +50,7 @@ class _CEntry(ctypes.Structure):
         ("uid", ctypes.c_int64), ("gid", ctypes.c_int64),
         ("typeflag", ctypes.c_uint8),
         ("data", ctypes.c_void_p),
+        ("linkname", ctypes.c_char_p), ("linkname_len", ctypes.c_size_t),
     ]
 
 
@@ -98,6 +99,7 @@ class Entry:
     gname: bytes = b""
     typeflag: int = ord("0")
     data: object = b""   # bytes / bytearray / memoryview / numpy uint8 array of `size` bytes
+    linkname: bytes = b""  # hdr.Linkname for typeflag '1' / '2' (docker's build-context dialect only)
 
     def __post_init__(self):
         if isinstance(self.name, str):
@@ -106,6 +108,8 @@ class Entry:
             self.uname = self.uname.encode("utf-8", "surrogateescape")
         if isinstance(self.gname, str):
             self.gname = self.gname.encode("utf-8", "surrogateescape")
+        if isinstance(self.linkname, str):
+            self.linkname = self.linkname.encode("utf-8", "surrogateescape")
 
 
 def _data_ptr(d, keep: list) -> Optional[int]:
@@ -131,7 +135,8 @@ def _to_c(entries: Sequence[Entry]):
     arr = (_CEntry * max(1, len(entries)))()
     for i, e in enumerate(entries):
         c = arr[i]
-        keep.extend((e.name, e.uname, e.gname))
+        keep.extend((e.name, e.uname, e.gname, e.linkname))
+        c.linkname, c.linkname_len = e.linkname, len(e.linkname)
         c.name, c.name_len = e.name, len(e.name)
         c.uname, c.uname_len = e.uname, len(e.uname)
         c.gname, c.gname_len = e.gname, len(e.gname)

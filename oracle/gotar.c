@@ -181,7 +181,7 @@ static size_t pax_record(const char *k, const char *v, size_t vlen, char *out) {
 
 typedef struct {
   int need_pax;     /* USTAR cannot hold it */
-  int has_path, has_uname, has_gname, has_uid, has_gid, has_size, has_mtime;
+  int has_path, has_uname, has_gname, has_uid, has_gid, has_size, has_mtime, has_linkpath;
   char uid_s[24], gid_s[24], size_s[24], mtime_s[24];
   size_t ustar_prefix_len; /* >0 when splitUSTARPath succeeded */
   int64_t mtime_rounded;
@@ -191,7 +191,8 @@ typedef struct {
  * AccessTime/ChangeTime are zeroed by WriteHeader because Format is FormatUnknown). */
 static int plan_entry(const gotar_entry *e, plan_t *p) {
   memset(p, 0, sizeof *p);
-  if (e->typeflag != '0' && e->typeflag != '5') return GOTAR_E_TYPE;
+  const int link = e->typeflag == '1' || e->typeflag == '2';
+  if (e->typeflag != '0' && e->typeflag != '5' && !link) return GOTAR_E_TYPE;
   /* WriteHeader: ModTime.Round(time.Second): half rounds up */
   p->mtime_rounded = e->mtime_sec + (e->mtime_nsec >= 500000000u ? 1 : 0);
 
@@ -202,6 +203,11 @@ static int plan_entry(const gotar_entry *e, plan_t *p) {
     if (!split_ustar_path(e->name, e->name_len, &pl)) ustar_ok = 0;
     else p->ustar_prefix_len = pl;
     p->has_path = 1;
+  }
+  /* verifyString(h.Linkname, 100, paxLinkpath): only paxPath may be split for USTAR */
+  if (link && (!is_ascii(e->linkname, e->linkname_len) || e->linkname_len > NAME_SIZE)) {
+    ustar_ok = 0;
+    p->has_linkpath = 1;
   }
   /* verifyString(h.Uname / h.Gname, 32, paxUname / paxGname) */
   if (!is_ascii(e->uname, e->uname_len) || e->uname_len > 32) {
@@ -239,10 +245,10 @@ static int plan_entry(const gotar_entry *e, plan_t *p) {
   /* header-only / trailing-slash / negative-size checks */
   if (e->typeflag == '0' && e->name_len > 0 && e->name[e->name_len - 1] == '/') return GOTAR_E_HEADER;
   if (e->size < 0) return GOTAR_E_HEADER; /* negative size: ErrHeader for files; tar.go never sets it for dirs */
-  if (e->typeflag == '5' && e->size != 0) return GOTAR_E_HEADER; /* tar.go: FileInfoHeader leaves Size 0 for dirs */
+  if ((e->typeflag == '5' || link) && e->size != 0) return GOTAR_E_HEADER; /* FileInfoHeader leaves Size 0 for dirs and links */
   /* validPAXRecord: NUL not allowed in path/uname/gname values */
   if ((p->has_path && has_nul(e->name, e->name_len)) || (p->has_uname && has_nul(e->uname, e->uname_len)) ||
-      (p->has_gname && has_nul(e->gname, e->gname_len)))
+      (p->has_gname && has_nul(e->gname, e->gname_len)) || (p->has_linkpath && has_nul(e->linkname, e->linkname_len)))
     pax_ok = 0;
   if (ustar_ok) {
     p->need_pax = 0;
@@ -253,13 +259,14 @@ static int plan_entry(const gotar_entry *e, plan_t *p) {
   return GOTAR_OK;
 }
 
-/* sorted keys: gid, gname, mtime, path, size, uid, uname (sort.Strings in writePAXHeader) */
+/* sorted keys: gid, gname, linkpath, mtime, path, size, uid, uname (sort.Strings in writePAXHeader) */
 static size_t pax_records(const gotar_entry *e, const plan_t *p, char *out) {
   size_t w = 0;
 #define REC(cond, key, val, vlen)                           \
   if (cond) w += pax_record(key, val, vlen, out ? out + w : NULL)
   REC(p->has_gid, "gid", p->gid_s, strlen(p->gid_s));
   REC(p->has_gname, "gname", e->gname, e->gname_len);
+  REC(p->has_linkpath, "linkpath", e->linkname, e->linkname_len);
   REC(p->has_mtime, "mtime", p->mtime_s, strlen(p->mtime_s));
   REC(p->has_path, "path", e->name, e->name_len);
   REC(p->has_size, "size", p->size_s, strlen(p->size_s));
@@ -300,8 +307,16 @@ int gotar_stream_size(const gotar_entry *es, size_t n, size_t *out) {
 static void template_v7plus(uint8_t *blk, const gotar_entry *e, const plan_t *p, const char *name, size_t name_len,
                             int to_ascii_strings) {
   memset(blk, 0, BLOCK);
-  char *tmp = (char *)malloc(name_len + e->uname_len + e->gname_len + 8);
+  char *tmp = (char *)malloc(name_len + e->uname_len + e->gname_len + e->linkname_len + 8);
   blk[156] = e->typeflag;
+  if (e->typeflag == '1' || e->typeflag == '2') {
+    if (to_ascii_strings) {
+      size_t n = to_ascii(e->linkname, e->linkname_len, tmp);
+      format_string(blk + 157, 100, tmp, n);
+    } else {
+      format_string(blk + 157, 100, e->linkname, e->linkname_len);
+    }
+  }
   if (to_ascii_strings) {
     size_t n = to_ascii(name, name_len, tmp);
     format_string(blk + 0, 100, tmp, n);

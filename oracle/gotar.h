@@ -38,8 +38,11 @@ typedef struct gotar_entry {
   int64_t mode;                            /* perm | setuid 04000 | setgid 02000 | sticky 01000,
                                               or RemoteMode when indexed (tar.go:246-250,287-291) */
   int64_t uid, gid;                        /* stat uid/gid or RemoteUID/RemoteGID                 */
-  uint8_t typeflag;                        /* '0' regular file, '5' (empty) directory            */
+  uint8_t typeflag;                        /* '0' regular file, '5' (empty) directory; docker's
+                                              build-context dialect also '1' hard link, '2' symlink */
   const uint8_t *data;                     /* size bytes of payload (io.Copy, tar.go:298)        */
+  const char *linkname; size_t linkname_len; /* hdr.Linkname for '1' / '2' (docker pkg/archive
+                                              addTarFile: os.Readlink / the first name of the inode) */
 } gotar_entry;
 
 enum {
