@@ -172,11 +172,23 @@ fcrc_join_kernel(const FileCrcEntry *__restrict__ files, uint32_t n, const uint8
   const uint64_t body = (size - head) & ~15ull;
   const uint32_t tail = (uint32_t)(size - head - body);
   const uint32_t u0 = first[f], nu = first[f + 1] - u0;
+  // Each lane folds a contiguous stretch of units Horner style (one multiplication per unit: by x^(8 * length of
+  // the unit it takes in), then moves its remainder to the end of the file with one x^(8n).
   uint32_t acc = 0;
-  for (uint32_t k = lane; k < nu; k += 32) {
-    uint64_t end = (uint64_t)(k + 1) * kFileCrcUnit;
-    if (end > body) end = body;
-    acc ^= crc_mul(raw[u0 + k], crc_xpow8((body - end) + tail));
+  if (nu) {
+    const uint32_t per = (nu + 31) / 32;
+    const uint32_t lo = lane * per, hi = lo + per < nu ? lo + per : nu;
+    if (lo < hi) {
+      const uint32_t k_full = crc_xpow8(kFileCrcUnit);
+      const uint64_t last_len = body - (uint64_t)(nu - 1) * kFileCrcUnit;
+      for (uint32_t k = lo; k < hi; k++) {
+        const uint32_t mult = (k == nu - 1) ? crc_xpow8(last_len) : k_full;
+        acc = (k == lo ? 0u : crc_mul(acc, mult)) ^ raw[u0 + k];
+      }
+      uint64_t end = (uint64_t)hi * kFileCrcUnit;
+      if (end > body) end = body;
+      acc = crc_mul(acc, crc_xpow8((body - end) + tail));
+    }
   }
   for (int o = 16; o > 0; o >>= 1) acc ^= __shfl_xor_sync(0xffffffffu, acc, o);
   if (lane == 0) {

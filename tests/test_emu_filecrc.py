@@ -68,3 +68,9 @@ def test_range_error():
     ent[1]["data_off"] = arena.size - 5
     rc, _ = emu_file_crc32(ent, arena)
     assert rc == -2          # -(1 + index of the bad entry)
+
+
+def test_more_units_than_lanes():
+    ent, arena = make([2_300_007, 70_000, 0, 5 * 65536], 21)      # 36 units: two per lane in the join, a full-unit tail
+    rc, crcs = emu_file_crc32(ent, arena)
+    assert rc == 0 and [int(c) for c in crcs] == expect(ent, arena)
