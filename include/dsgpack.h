@@ -78,7 +78,8 @@ typedef struct dsg_ctx dsg_ctx; /* opaque */
 typedef struct dsg_opts {
   uint32_t struct_size;    /* sizeof(dsg_opts), for forward compatibility                           */
   int32_t level;           /* DSG_LEVEL_DEFAULT or DSG_LEVEL_STORED                                  */
-  uint64_t segment_bytes;  /* tar-stream bytes per pipeline segment (0 = default 256 MiB)            */
+  uint64_t segment_bytes;  /* tar-stream bytes per pipeline segment (0 = a sixth of the stream,
+                            * between 64 and 512 MiB)                                            */
   uint32_t flags;          /* DSG_F_*                                                                */
   uint32_t reserved;
 } dsg_opts;

@@ -71,7 +71,8 @@ int emu_lz_deflate(const uint8_t *in, uint64_t len, const uint8_t *dict, uint32_
   }
   const uint32_t nchunks = (uint32_t)((len + kChunk - 1) / kChunk);
   if (run_chunks == 0) run_chunks = 1;
-  const uint32_t nruns = (nchunks + run_chunks - 1) / run_chunks;
+  const uint32_t big_runs = nchunks / run_chunks;  // the remainder goes chunk by chunk (the tail tickets)
+  const uint32_t nruns = big_runs + (nchunks - big_runs * run_chunks);
   if (grid == 0 || grid > nruns) grid = nruns;
   std::vector<uint8_t> slots((size_t)nchunks * kSlotBytes, 0xAB);
   std::vector<uint32_t> meta(nchunks, 0);
@@ -88,6 +89,7 @@ int emu_lz_deflate(const uint8_t *in, uint64_t len, const uint8_t *dict, uint32_
   P.chunk_meta = meta.data();
   P.nchunks = nchunks;
   P.run_chunks = run_chunks;
+  P.big_runs = big_runs;
   P.ticket = &ticket;
   P.tok_scratch = tok.data();
   P.prof = nullptr;
