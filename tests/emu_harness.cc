@@ -154,4 +154,10 @@ int emu_file_crc32(const uint8_t *entries, uint32_t n, uint32_t stride, uint32_t
   return 0;
 }
 
+// Serial Huffman length construction (huffman.cuh: two-queue merge + zlib gen_bitlen repair), for the Kraft tests.
+int emu_huff_lengths(const uint32_t *freq, int n, int max_bits, uint8_t *lens) {
+  static HuffScratch S;
+  return huff_build_lengths(freq, n, max_bits, lens, S);
+}
+
 }  // extern "C"

@@ -110,3 +110,23 @@ def test_emulated_crc32_unaligned_pointer():
     for off in (1, 5, 9, 13):
         got = _lib().emu_crc32(ctypes.c_void_p(data.ctypes.data + off), ctypes.c_uint64(150_000))
         assert got == zlib.crc32(data[off:off + 150_000].tobytes())
+
+
+@pytest.mark.parametrize("sched", ["reverse", "random"])
+def test_emulated_deflate_under_other_thread_schedules(sched):
+    """The emulator normally runs the threads of a block in thread-id order, which hides code that relies on that
+    order (atomics "arriving" in stream order, a missing barrier). EMU_SCHED is read once per process: subprocess."""
+    import os
+    import subprocess
+    import sys
+    code = (
+        "import sys, zlib; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "import test_emu_deflate as t\n"
+        "for name in ('mixed_100k', 'text_140k', 'tile_edges', 'zeros_70k'):\n"
+        "    d = t.CASES[name]; z = t.emu_deflate(d, grid=2, run_chunks=2)\n"
+        "    assert zlib.decompress(z, -15) == d, name\n"
+        "    assert len(z) <= 1.05 * t.zlib6(d) + 512, (name, len(z))\n"
+        "print('ok')\n" % (helpers.ROOT, os.path.join(helpers.ROOT, "tests")))
+    env = dict(os.environ, EMU_SCHED=sched)
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=900)
+    assert r.returncode == 0 and r.stdout.strip() == "ok", r.stderr[-2000:]
