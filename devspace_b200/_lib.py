@@ -19,7 +19,7 @@ DSG_F_NO_TRAILER = 1
 SYMBOLS = [
     "dsg_abi_version", "dsg_strerror", "dsg_device_count", "dsg_last_error", "dsg_ctx_create", "dsg_ctx_destroy",
     "dsg_pinned_alloc", "dsg_pinned_free", "dsg_entry_header_bytes", "dsg_tar_size", "dsg_gzip_bound",
-    "dsg_shard_bounds", "dsg_pack", "dsg_pack_tar_only", "dsg_pack_device", "dsg_get_stats", "dsg_dev_tar_build",
+    "dsg_shard_bounds", "dsg_stitch_members", "dsg_pack", "dsg_pack_tar_only", "dsg_pack_device", "dsg_get_stats", "dsg_dev_tar_build",
     "dsg_dev_crc32", "dsg_dev_deflate", "dsg_dev_gzip", "dsg_dev_alloc", "dsg_dev_free", "dsg_dev_upload",
     "dsg_dev_download", "dsg_crc32_noalloc", "dsg_file_crc32", "dsg_dev_file_crc32", "dsg_directory_hash", "dsg_docker_context_tar", "dsg_walk", "dsg_written_count", "dsg_written_get",
     "dsg_written_entries", "dsg_written_free", "dsg_write_tar",

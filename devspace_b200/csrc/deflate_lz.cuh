@@ -178,6 +178,30 @@ DSG_D void handoff_wait(int bar) {
 #endif
 }
 
+// Shared-memory loads through 32-bit shared-window addresses. Inside the chain-walk loops the compiler otherwise
+// keeps the arrays as generic pointers and rebuilds the window base (S2UR/ULEA) in every iteration.
+#if defined(DSG_EMU)
+struct SmemBase { const uint8_t *p; };
+DSG_D SmemBase smem_base(const void *p) { return SmemBase{static_cast<const uint8_t *>(p)}; }
+DSG_D uint32_t lds_u8(SmemBase b, uint32_t off) { return b.p[off]; }
+DSG_D uint32_t lds_u16(SmemBase b, uint32_t off) {
+  return (uint32_t)b.p[off] | ((uint32_t)b.p[off + 1] << 8);
+}
+#else
+struct SmemBase { uint32_t a; };
+DSG_D SmemBase smem_base(const void *p) { return SmemBase{(uint32_t)__cvta_generic_to_shared(p)}; }
+DSG_D uint32_t lds_u8(SmemBase b, uint32_t off) {
+  uint32_t v;
+  asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(b.a + off));
+  return v;
+}
+DSG_D uint32_t lds_u16(SmemBase b, uint32_t off) {
+  uint32_t v;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(b.a + off));
+  return v;
+}
+#endif
+
 DSG_D uint32_t hash4(uint32_t v) { return (v * 2654435761u) >> (32 - kHashBits); }
 
 // 4 bytes at an arbitrary shared-memory byte offset (little endian)
@@ -600,6 +624,7 @@ constexpr int kChase = 4;
 
 DSG_D void refine_search(const uint8_t *s_data, const uint16_t *s_prev, uint8_t *s_mlen, uint16_t *s_mdist,
                          const uint16_t *s_work, uint32_t nwork, int tile_rp, int chunk_end, int lo_rp, uint32_t *ctr) {
+  const SmemBase sd = smem_base(s_data), sp = smem_base(s_prev);
   for (;;) {
     const uint32_t k = atomicAdd(ctr, 1u);
     if (k >= nwork) break;
@@ -623,10 +648,10 @@ DSG_D void refine_search(const uint8_t *s_data, const uint16_t *s_prev, uint8_t 
       uint32_t c[kChase + 1];
       c[0] = q;
 #pragma unroll
-      for (int i = 0; i < kChase; i++) c[i + 1] = c[i] == kNil ? (uint32_t)kNil : (uint32_t)s_prev[c[i]];
+      for (int i = 0; i < kChase; i++) c[i + 1] = c[i] == kNil ? (uint32_t)kNil : lds_u16(sp, 2u * c[i]);
       uint32_t f[kChase];
 #pragma unroll
-      for (int i = 0; i < kChase; i++) f[i] = s_data[(c[i] == kNil ? 0u : c[i]) + best];
+      for (int i = 0; i < kChase; i++) f[i] = lds_u8(sd, (c[i] == kNil ? 0u : c[i]) + (uint32_t)best);
       bool stop = false;
       uint32_t nq = c[kChase];
 #pragma unroll

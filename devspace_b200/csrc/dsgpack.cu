@@ -589,6 +589,48 @@ int dsg_tar_size(const dsg_entry *entries, size_t n, const char *strtab, size_t 
 
 uint64_t dsg_gzip_bound(uint64_t tar_bytes) { return 18 + lz_deflate_bound(tar_bytes); }
 
+// The shards' gzip members as ONE member ("optional host-side stitch" for decoders that stop after
+// the first member): every deflate body this library writes consists of non-final blocks that end on a byte
+// boundary plus the 2-byte terminator 03 00 (an empty final block), so the bodies of all members but the last lose
+// their terminator and are concatenated; the checksum is folded with x^(8n) mod P like the tile remainders on the
+// device, ISIZE is the sum mod 2^32. Host integer work over O(number of shards) headers; the bodies are copied once.
+int dsg_stitch_members(const uint8_t *const *members, const size_t *member_lens, const uint64_t *tar_lens, size_t n,
+                       uint8_t *out, size_t out_cap, size_t *out_len) {
+  static const uint8_t hdr[10] = {0x1f, 0x8b, 0x08, 0, 0, 0, 0, 0, 0, 0xff};
+  if (!members || !member_lens || !tar_lens || !out_len || n == 0) return DSG_E_ARG;
+  size_t need = 10 + 8;
+  for (size_t i = 0; i < n; i++) {
+    const uint8_t *m = members[i];
+    const size_t len = member_lens[i];
+    if (!m || len < 20 || memcmp(m, hdr, 10) != 0) return DSG_E_ARG;              // not one of our members
+    if (m[len - 10] != 0x03 || m[len - 9] != 0x00) return DSG_E_ARG;              // body must end with the terminator
+    uint32_t isize = 0;
+    for (int b = 0; b < 4; b++) isize |= (uint32_t)m[len - 4 + b] << (8 * b);
+    if (isize != (uint32_t)tar_lens[i]) return DSG_E_ARG;                          // tar_lens does not belong to it
+    need += len - 18 - (i + 1 < n ? 2 : 0);
+  }
+  *out_len = need;
+  if (!out || out_cap < need) return DSG_E_CAPACITY;
+  memcpy(out, hdr, 10);
+  size_t w = 10;
+  uint32_t crc = 0;
+  uint64_t total = 0;
+  for (size_t i = 0; i < n; i++) {
+    const uint8_t *m = members[i];
+    const size_t len = member_lens[i];
+    const size_t body = len - 18 - (i + 1 < n ? 2 : 0);
+    memcpy(out + w, m + 10, body);
+    w += body;
+    uint32_t c = 0;
+    for (int b = 0; b < 4; b++) c |= (uint32_t)m[len - 8 + b] << (8 * b);
+    crc = total ? crc_combine(crc, c, tar_lens[i]) : c;
+    total += tar_lens[i];
+  }
+  for (int b = 0; b < 4; b++) out[w + b] = (uint8_t)(crc >> (8 * b));
+  for (int b = 0; b < 4; b++) out[w + 4 + b] = (uint8_t)((uint32_t)total >> (8 * b));
+  return DSG_OK;
+}
+
 int dsg_shard_bounds(const dsg_entry *entries, size_t n, const char *strtab, size_t strtab_len, int nshards,
                      uint64_t *bounds) {
   if ((!entries && n) || !strtab || !bounds || nshards <= 0) return DSG_E_ARG;

@@ -136,6 +136,16 @@ int dsg_tar_size(const dsg_entry *entries, size_t n, const char *strtab, size_t 
 /* Upper bound of the gzip output for a tar stream of `tar_bytes` bytes (for sizing `out`). */
 uint64_t dsg_gzip_bound(uint64_t tar_bytes);
 
+/* One gzip member out of the shards' members (for decoders that stop after the first member; GNU
+ * gzip/tar and CPython read the plain concatenation as well). members[i] / member_lens[i]: the output of dsg_pack
+ * for shard i, in shard order; tar_lens[i]: that shard's tar-stream length (dsg_tar_size with the shard's flags, or
+ * dsg_stats.tar_bytes). Host work only, no context: strips the inner headers, trailers and block terminators and
+ * folds the checksums (the crc32_combine identity). DSG_E_CAPACITY with *out_len = the size needed; DSG_E_ARG when
+ * a piece is not a member this library wrote or tar_lens[i] does not match its ISIZE. No counterpart in the
+ * reference (it writes one member with one writer). */
+int dsg_stitch_members(const uint8_t *const *members, const size_t *member_lens, const uint64_t *tar_lens, size_t n,
+                       uint8_t *out, size_t out_cap, size_t *out_len);
+
 /* Contiguous entry ranges balanced by tar-stream bytes for `nshards` GPUs:
  * shard s owns entries [bounds[s], bounds[s+1]). `bounds` has nshards+1 slots. Files are never split. */
 int dsg_shard_bounds(const dsg_entry *entries, size_t n, const char *strtab, size_t strtab_len, int nshards,
