@@ -19,7 +19,7 @@ DSG_F_NO_TRAILER = 1
 SYMBOLS = [
     "dsg_abi_version", "dsg_strerror", "dsg_device_count", "dsg_last_error", "dsg_ctx_create", "dsg_ctx_destroy",
     "dsg_pinned_alloc", "dsg_pinned_free", "dsg_entry_header_bytes", "dsg_tar_size", "dsg_gzip_bound",
-    "dsg_shard_bounds", "dsg_stitch_members", "dsg_pack", "dsg_pack_tar_only", "dsg_pack_device", "dsg_get_stats", "dsg_dev_tar_build",
+    "dsg_shard_bounds", "dsg_stitch_members", "dsg_pack", "dsg_pack_tar_only", "dsg_pack_fd", "dsg_pack_device", "dsg_get_stats", "dsg_dev_tar_build",
     "dsg_dev_crc32", "dsg_dev_deflate", "dsg_dev_gzip", "dsg_dev_alloc", "dsg_dev_free", "dsg_dev_upload",
     "dsg_dev_download", "dsg_crc32_noalloc", "dsg_file_crc32", "dsg_dev_file_crc32", "dsg_directory_hash", "dsg_docker_context_tar", "dsg_walk", "dsg_written_count", "dsg_written_get",
     "dsg_written_entries", "dsg_written_free", "dsg_write_tar",
@@ -90,6 +90,7 @@ def load(build_if_missing: bool = True):
     lib.dsg_pack.argtypes = pack_args
     lib.dsg_pack_tar_only.argtypes = pack_args
     lib.dsg_pack_device.argtypes = pack_args
+    lib.dsg_pack_fd.argtypes = [vp, vp, sz, vp, sz, vp, sz, c_int, c_int, u64p]
     lib.dsg_get_stats.argtypes = [vp, POINTER(DsgStats)]
     lib.dsg_dev_tar_build.argtypes = [vp, vp, sz, vp, sz, vp, sz, c_uint32, vp, sz, u64p]
     lib.dsg_dev_crc32.argtypes = [vp, vp, sz, POINTER(c_uint32)]

@@ -171,12 +171,7 @@ extern "C" int dsg_docker_context_tar(dsg_ctx *ctx, const char *src_path, dsg_ex
   int rc = dsg_tar_size(c.entries.data(), c.entries.size(), strtab, c.strtab.size(), 0, &T);
   if (rc) return fail(rc, std::string("archive/tar: ") + dsg_strerror(rc));
   uint8_t *arena = (uint8_t *)dsg_pinned_alloc(ctx, (size_t)c.arena_bytes + 16);
-  uint8_t *out = (uint8_t *)dsg_pinned_alloc(ctx, (size_t)T + 16);
-  if (!arena || !out) {
-    if (arena) dsg_pinned_free(ctx, arena);
-    if (out) dsg_pinned_free(ctx, out);
-    return fail(DSG_E_NOMEM, "pinned allocation failed");
-  }
+  if (!arena) return fail(DSG_E_NOMEM, "pinned allocation failed");
   for (size_t i = 0; i < c.entries.size() && rc == DSG_OK; i++) {
     if (c.paths[i].empty()) continue;
     const dsg_entry &e = c.entries[i];
@@ -192,31 +187,20 @@ extern "C" int dsg_docker_context_tar(dsg_ctx *ctx, const char *src_path, dsg_ex
     }
     if (got != (uint64_t)e.size) rc = fail(DSG_E_HEADER, "archive/tar: " + c.paths[i] + ": file changed size");
   }
-  size_t n = 0;
-  if (rc == DSG_OK) {
-    rc = dsg_pack_tar_only(ctx, c.entries.data(), c.entries.size(), strtab, c.strtab.size(), arena,
-                           (size_t)c.arena_bytes, out, (size_t)T + 16, &n);
-    if (rc) fail(rc, dsg_last_error(ctx));
-  }
+  uint64_t n = 0;
   if (rc == DSG_OK) {
     const int fd = open(out_path, O_WRONLY | O_CREAT | O_TRUNC, 0600);
     if (fd < 0) {
       rc = fail(DSG_E_ARG, std::string("open ") + out_path + ": " + strerror(errno));
     } else {
-      size_t done = 0;
-      while (done < n) {
-        const ssize_t k = write(fd, out + done, n - done);
-        if (k <= 0) {
-          rc = fail(DSG_E_ARG, std::string("write ") + out_path + ": " + strerror(errno));
-          break;
-        }
-        done += (size_t)k;
-      }
+      rc = dsg_pack_fd(ctx, c.entries.data(), c.entries.size(), strtab, c.strtab.size(), arena, (size_t)c.arena_bytes,
+                       fd, 0, &n);  // uncompressed: what TarWithOptions pipes to the daemon
+      if (rc) fail(rc, dsg_last_error(ctx));
       close(fd);
+      if (rc == DSG_OK && n != T) rc = fail(DSG_E_CUDA, "internal: stream length differs from the plan");
     }
   }
   dsg_pinned_free(ctx, arena);
-  dsg_pinned_free(ctx, out);
   if (rc == DSG_OK) {
     if (tar_bytes) *tar_bytes = n;
     if (n_entries) *n_entries = c.entries.size();

@@ -9,6 +9,8 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <errno.h>
+#include <unistd.h>
 
 #include <algorithm>
 #include <mutex>
@@ -85,6 +87,8 @@ struct dsg_ctx {
   DevBuf slot_arena[2], slot_tar[2], slot_out[2], seg_ranges;
   Timer tim[kTimCount];
   uint64_t *h_scalars = nullptr;  // pinned mirror of `scalars`
+  uint8_t *h_stage[2] = {nullptr, nullptr};  // pinned staging of the file-descriptor sink (dsg_pack_fd)
+  size_t h_stage_cap = 0;
   uint32_t launches = 0;
   int sm_count = 148;
 };
@@ -509,6 +513,8 @@ void dsg_ctx_destroy(dsg_ctx *ctx) {
     if (t.b) cudaEventDestroy(t.b);
   }
   if (ctx->h_scalars) cudaFreeHost(ctx->h_scalars);
+  for (uint8_t *b : ctx->h_stage)
+    if (b) cudaFreeHost(b);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   if (ctx->stream_in) cudaStreamDestroy(ctx->stream_in);
   if (ctx->stream_out) cudaStreamDestroy(ctx->stream_out);
@@ -944,8 +950,21 @@ int dsg_pack_device(dsg_ctx *ctx, const dsg_entry *d_entries, size_t n, const ch
 // Two device slots per buffer kind; the host only blocks on the per-segment size read-back.
 static int pack_host_pipelined(dsg_ctx *ctx, const dsg_entry *entries, size_t n, const char *strtab, size_t strtab_len,
                                const uint8_t *arena, size_t arena_len, bool gzip, uint8_t *out, size_t out_cap,
-                               size_t *out_len) {
+                               size_t *out_len, int sink_fd = -1) {
+  // sink_fd >= 0: the stream goes to that file descriptor instead of `out`: every segment is copied into one of two
+  // pinned staging buffers and written while the GPU works on the following segments.
   constexpr int NS = 2;
+  const bool sink = sink_fd >= 0;
+  auto write_all = [&](const void *buf, size_t nbytes) -> bool {
+    const uint8_t *q = static_cast<const uint8_t *>(buf);
+    while (nbytes) {
+      const ssize_t k = write(sink_fd, q, nbytes);
+      if (k <= 0) return false;
+      q += k;
+      nbytes -= (size_t)k;
+    }
+    return true;
+  };
   cudaStream_t s_cmp = ctx->stream, s_in = ctx->stream_in, s_out = ctx->stream_out;
   CU(cudaEventRecord(ctx->tim[kTimTotal].a, s_cmp));
   // ---- manifest + plan ---------------------------------------------------------------------------------------
@@ -998,14 +1017,30 @@ static int pack_host_pipelined(dsg_ctx *ctx, const dsg_entry *entries, size_t n,
   const uint64_t seg_out_cap = gzip ? lz_deflate_bound(std::min(S, std::max<uint64_t>(T, 1))) : 0;
   size_t produced = 0;
   if (gzip) {
-    if (out_cap < 18) {
-      *out_len = (size_t)dsg_gzip_bound(T);
-      return fail(ctx, DSG_E_CAPACITY, "gzip output needs at least 18 bytes");
-    }
     static const uint8_t hdr[10] = {0x1f, 0x8b, 0x08, 0, 0, 0, 0, 0, 0, 0xff};  // compress/gzip Writer defaults
-    memcpy(out, hdr, 10);
+    if (sink) {
+      if (!write_all(hdr, 10)) return fail(ctx, DSG_E_ARG, "write: %s", strerror(errno));
+    } else {
+      if (out_cap < 18) {
+        *out_len = (size_t)dsg_gzip_bound(T);
+        return fail(ctx, DSG_E_CAPACITY, "gzip output needs at least 18 bytes");
+      }
+      memcpy(out, hdr, 10);
+    }
     produced = 10;
   }
+  if (sink) {
+    const size_t want = (size_t)(gzip ? seg_out_cap : std::min(S, std::max<uint64_t>(T, 1))) + 64;
+    if (want > ctx->h_stage_cap) {
+      for (uint8_t *&b : ctx->h_stage) {
+        if (b) cudaFreeHost(b);
+        b = nullptr;
+        CU(cudaHostAlloc(reinterpret_cast<void **>(&b), want, cudaHostAllocDefault));
+      }
+      ctx->h_stage_cap = want;
+    }
+  }
+  std::vector<uint64_t> seg_bytes(nseg, 0);
   // ---- slots ---------------------------------------------------------------------------------------------------
   for (int k = 0; k < NS; k++) {
     CU(ctx->slot_arena[k].ensure(max_arena + 64));
@@ -1112,7 +1147,8 @@ static int pack_host_pipelined(dsg_ctx *ctx, const dsg_entry *entries, size_t n,
     CUP(cudaEventSynchronize(ev_cmp[i]));
     const uint64_t nbytes = gzip ? h_sizes[i % kMaxSegSizes] : hi - lo;
     const uint64_t tail = gzip && i + 1 == nseg ? 8 : 0;
-    if (produced + nbytes + tail > out_cap) {
+    seg_bytes[i] = nbytes;
+    if (!sink && produced + nbytes + tail > out_cap) {
       produced += nbytes + tail;
       status = DSG_E_CAPACITY;
       CUP(cudaEventRecord(ev_out[i], s_out));
@@ -1121,18 +1157,31 @@ static int pack_host_pipelined(dsg_ctx *ctx, const dsg_entry *entries, size_t n,
     CUP(cudaStreamWaitEvent(s_out, ev_cmp[i], 0));
     const void *src = gzip ? ctx->slot_out[k].p : ctx->slot_tar[k].p;
     if (nbytes && status == DSG_OK) {
-      CUP(cudaMemcpyAsync(out + produced, src, nbytes, cudaMemcpyDeviceToHost, s_out));
+      CUP(cudaMemcpyAsync(sink ? ctx->h_stage[i % 2] : out + produced, src, nbytes, cudaMemcpyDeviceToHost, s_out));
       d2h += nbytes;
     }
     produced += nbytes;
     CUP(cudaEventRecord(ev_out[i], s_out));
     return DSG_OK;
   };
+  auto flush = [&](uint32_t j) -> int {  // file-descriptor sink: segment j has arrived in its staging buffer
+    if (!sink) return DSG_OK;
+    CUP(cudaEventSynchronize(ev_out[j]));
+    if (!write_all(ctx->h_stage[j % 2], (size_t)seg_bytes[j])) {
+      cudaDeviceSynchronize();
+      destroy_events();
+      return fail(ctx, DSG_E_ARG, "write: %s", strerror(errno));
+    }
+    return DSG_OK;
+  };
   for (uint32_t i = 0; i < nseg && rc == DSG_OK; i++) {
     rc = enqueue(i);
+    if (rc == DSG_OK && i >= 2) rc = flush(i - 2);  // written while segments i-1 and i are on the GPU
     if (rc == DSG_OK && i >= 1) rc = drain(i - 1);
   }
+  if (rc == DSG_OK && nseg >= 2) rc = flush(nseg - 2);
   if (rc == DSG_OK) rc = drain(nseg - 1);
+  if (rc == DSG_OK) rc = flush(nseg - 1);
   if (rc != DSG_OK) {
     cudaDeviceSynchronize();
     destroy_events();
@@ -1160,8 +1209,14 @@ static int pack_host_pipelined(dsg_ctx *ctx, const dsg_entry *entries, size_t n,
     const uint32_t crc = cs[0], isize = cs[1];
     ctx->stats.crc32 = crc;
     if (status == DSG_OK) {
-      for (int b = 0; b < 4; b++) out[produced + b] = (uint8_t)(crc >> (8 * b));
-      for (int b = 0; b < 4; b++) out[produced + 4 + b] = (uint8_t)(isize >> (8 * b));
+      uint8_t tr[8];
+      for (int b = 0; b < 4; b++) tr[b] = (uint8_t)(crc >> (8 * b));
+      for (int b = 0; b < 4; b++) tr[4 + b] = (uint8_t)(isize >> (8 * b));
+      if (sink) {
+        if (!write_all(tr, 8)) return fail(ctx, DSG_E_ARG, "write: %s", strerror(errno));
+      } else {
+        memcpy(out + produced, tr, 8);
+      }
     }
     produced += 8;
     if (ctx->h_scalars[kSSpare] != 0 && status == DSG_OK)
@@ -1196,6 +1251,18 @@ int dsg_pack(dsg_ctx *ctx, const dsg_entry *entries, size_t n, const char *strta
 int dsg_pack_tar_only(dsg_ctx *ctx, const dsg_entry *entries, size_t n, const char *strtab, size_t strtab_len,
                       const uint8_t *arena, size_t arena_len, uint8_t *out, size_t out_cap, size_t *out_len) {
   return pack_host(ctx, entries, n, strtab, strtab_len, arena, arena_len, false, out, out_cap, out_len);
+}
+
+int dsg_pack_fd(dsg_ctx *ctx, const dsg_entry *entries, size_t n, const char *strtab, size_t strtab_len,
+                const uint8_t *arena, size_t arena_len, int fd, int gzip, uint64_t *out_len) {
+  if (!ctx || fd < 0 || (n && (!entries || !strtab)) || (arena_len && !arena) || n > 0xfffffff0ull) return DSG_E_ARG;
+  std::lock_guard<std::mutex> g(ctx->mu);
+  int rc = begin_call(ctx);
+  if (rc) return rc;
+  size_t produced = 0;
+  rc = pack_host_pipelined(ctx, entries, n, strtab, strtab_len, arena, arena_len, gzip != 0, nullptr, 0, &produced, fd);
+  if (out_len) *out_len = produced;
+  return rc;
 }
 
 int dsg_get_stats(const dsg_ctx *ctx, dsg_stats *out) {

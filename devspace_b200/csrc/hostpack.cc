@@ -280,37 +280,22 @@ int dsg_write_tar(dsg_ctx *ctx, const dsg_file_info *files, size_t nfiles, const
     dsg_written *h = nullptr;
     std::string err;
     int rc = dsg_walk(files, nfiles, cfg, &h);
-    uint8_t *arena = nullptr, *out = nullptr;
+    uint8_t *arena = nullptr;
     if (rc == DSG_OK) {
       Walked &w = h->w;
       const char *strtab = w.strtab.empty() ? "" : w.strtab.data();
       arena = (uint8_t *)dsg_pinned_alloc(ctx, (size_t)w.arena_bytes + 16);
       rc = arena ? read_all(w, arena, &err) : DSG_E_NOMEM;
-      uint64_t T = 0;
-      if (rc == DSG_OK) rc = dsg_tar_size(w.entries.data(), w.entries.size(), strtab, w.strtab.size(), 0, &T);
-      size_t cap = 0, n = 0;
+      // gzip.NewWriter(file) + tar.NewWriter: the stream goes to the temp file segment by segment while the GPU works
+      // on the next segments (dsg_pack_fd)
+      uint64_t nbytes = 0;
       if (rc == DSG_OK) {
-        cap = (size_t)dsg_gzip_bound(T);
-        out = (uint8_t *)dsg_pinned_alloc(ctx, cap);
-        rc = out ? dsg_pack(ctx, w.entries.data(), w.entries.size(), strtab, w.strtab.size(), arena,
-                            (size_t)w.arena_bytes, out, cap, &n)
-                 : DSG_E_NOMEM;
-      }
-      if (rc == DSG_OK) {
-        size_t done = 0;
-        while (done < n) {
-          ssize_t k = write(fd, out + done, n - done);
-          if (k <= 0) {
-            rc = DSG_E_ARG;
-            err = std::string("write temp file: ") + strerror(errno);
-            break;
-          }
-          done += (size_t)k;
-        }
+        rc = dsg_pack_fd(ctx, w.entries.data(), w.entries.size(), strtab, w.strtab.size(), arena,
+                         (size_t)w.arena_bytes, fd, 1, &nbytes);
+        if (rc != DSG_OK) err = dsg_last_error(ctx);
       }
     }
     if (arena) dsg_pinned_free(ctx, arena);
-    if (out) dsg_pinned_free(ctx, out);
     close(fd);
     if (rc == DSG_OK) {
       snprintf(out_path, out_path_cap, "%s", tmpl);

@@ -152,6 +152,14 @@ class Packer:
         self._check(rc)
         return n_out.value
 
+    def pack_to_fd(self, man: Manifest, fd: int, tar_only: bool = False) -> int:
+        """dsg_pack_fd: the stream goes to the file descriptor segment by segment, overlapped with the GPU work."""
+        n_out = ctypes.c_uint64()
+        rc = self._lib.dsg_pack_fd(self._ctx, _ptr(man.entries), man.n, _ptr(man.strtab), man.strtab.size,
+                                   _ptr(man.arena), man.arena.size, int(fd), 0 if tar_only else 1, byref(n_out))
+        self._check(rc)
+        return n_out.value
+
     def pack(self, man: Manifest, tar_only: bool = False) -> bytes:
         """writeTar's archive bytes for the manifest: gzip(tar stream) (or the bare tar stream)."""
         T = self.tar_size(man, 0)

@@ -165,6 +165,14 @@ int dsg_pack(dsg_ctx *ctx, const dsg_entry *entries, size_t n, const char *strta
 int dsg_pack_tar_only(dsg_ctx *ctx, const dsg_entry *entries, size_t n, const char *strtab, size_t strtab_len,
                       const uint8_t *arena, size_t arena_len, uint8_t *out, size_t out_cap, size_t *out_len);
 
+/* dsg_pack / dsg_pack_tar_only (gzip = 1 / 0) with the stream written to the file descriptor `fd` instead of a
+ * caller buffer: writeTar's temp file (tar.go:148-157; SURVEY.md 8f rank 3, "overlap D2H with the temp-file
+ * write"). Every pipeline segment lands in one of two pinned staging buffers of the context and is written while
+ * the GPU works on the following segments; no output bound has to be allocated. *out_len = bytes written. On an
+ * error part of the stream may have been written already (the caller removes the file, as tar.go:172 does). */
+int dsg_pack_fd(dsg_ctx *ctx, const dsg_entry *entries, size_t n, const char *strtab, size_t strtab_len,
+                const uint8_t *arena, size_t arena_len, int fd, int gzip, uint64_t *out_len);
+
 /* Device-resident variant of dsg_pack for callers that already hold manifest + arena in HBM
  * (bench.py's kernel-only number): every `d_` pointer is device memory on the context's device.
  * *out_len is written on the host after the call's own synchronisation. */

@@ -217,3 +217,38 @@ def test_level6_pack_device_and_capacity_error(packer6):
         dm.free()
         d_out.free()
         small.free()
+
+
+@pytest.mark.parametrize("tar_only", [False, True])
+def test_pack_to_fd_streams_the_same_bytes(tmp_path, tar_only):
+    """dsg_pack_fd: the segments reach the file through the staging buffers in order; the file
+    equals what dsg_pack returns, also with many small segments and with a single one."""
+    from devspace_b200.pack import Packer
+    es = SUITE["mixed_tree"]
+    man = from_entries(es)
+    ref = oracle.tar_stream(es)
+    for seg in (65536, 1 << 20, 0):
+        with Packer(level=6, segment_bytes=seg) as p:
+            path = tmp_path / ("o%d" % seg)
+            with open(path, "wb") as f:
+                n = p.pack_to_fd(man, f.fileno(), tar_only=tar_only)
+            st = p.stats()
+            mem = p.pack(man, tar_only=tar_only)
+        got = path.read_bytes()
+        assert n == len(got) and st["segments"] >= 1
+        assert (got if tar_only else gzip.decompress(got)) == ref
+        if seg != 65536 or tar_only:
+            assert got == mem
+    with Packer(level=6) as p:                      # an unusable descriptor is an error, not a crash
+        from devspace_b200._lib import DsgError
+        r, w = os.pipe()
+        os.close(r)
+        import signal
+        old = signal.signal(signal.SIGPIPE, signal.SIG_IGN)
+        try:
+            with pytest.raises(DsgError):
+                p.pack_to_fd(man, w)
+        finally:
+            signal.signal(signal.SIGPIPE, old)
+            os.close(w)
+        assert gzip.decompress(p.pack(man)) == ref  # the context is still usable
