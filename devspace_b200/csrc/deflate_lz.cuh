@@ -106,10 +106,10 @@ static_assert(kMaxDist % 16 == 0 && kLook % 16 == 0, "ring loads move 16-byte gr
 
 // misc[] slots
 enum { kMTicket = 0, kMStart, kMNTok, kMMode, kMOutLo, kMOutHi, kMHdrBits, kMChunkBytes, kMHlit, kMHdist, kMHclen,
-       kMNRle, kMBodyDyn, kMBodyFix, kMError, kMRunCtr /* kTeams slots */,
+       kMNRle, kMBodyDyn, kMBodyFix, kMError, kMRunCtr /* kTeams slots */, kMRunStart = kMRunCtr + kTeams,
        kMScan = 32 /* CTA scan: 32 warp partials + carry; team scans: 20 words each */, kMTeamScan = kMScan,
        kMTeamScanStride = 20 };
-static_assert(kMRunCtr + kTeams <= kMScan && kMTeamScan + kTeams * kMTeamScanStride <= 192, "misc[] slots");
+static_assert(kMRunStart < kMScan && kMTeamScan + kTeams * kMTeamScanStride <= 192, "misc[] slots");
 
 // Kernel parameter block
 struct LzParams {
@@ -271,6 +271,38 @@ DSG_D uint32_t group_exclusive_scan(uint32_t v, uint32_t *scratch, uint32_t *tot
   return r;
 }
 
+// Exclusive running maximum over the threads of a group (identity 0). `scratch` >= 17 words (33 for the CTA).
+DSG_D uint32_t group_exclusive_max(uint32_t v, uint32_t *scratch, uint32_t *total, const LzGroup &g) {
+  const uint32_t lane = (uint32_t)g.tid & 31, warp = (uint32_t)g.tid >> 5, nw = (uint32_t)g.n >> 5;
+  uint32_t x = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= (uint32_t)o) x = x > y ? x : y;
+  }
+  uint32_t ex = __shfl_up_sync(0xffffffffu, x, 1);
+  if (lane == 0) ex = 0;
+  if (lane == 31) scratch[warp] = x;
+  group_sync(g);
+  if (warp == 0) {
+    const uint32_t t = lane < nw ? scratch[lane] : 0;
+    uint32_t m = t;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t y = __shfl_up_sync(0xffffffffu, m, o);
+      if (lane >= (uint32_t)o) m = m > y ? m : y;
+    }
+    uint32_t before = __shfl_up_sync(0xffffffffu, m, 1);
+    if (lane == 0) before = 0;
+    if (lane < nw) scratch[lane] = before;
+    if (lane == nw - 1) scratch[nw] = m;
+  }
+  group_sync(g);
+  const uint32_t w = scratch[warp];
+  *total = scratch[nw];
+  return ex > w ? ex : w;
+}
+
 // Sequential LSB-first bit writer into a zeroed shared-memory window (single thread).
 struct SmemBitWriter {
   uint32_t *w;
@@ -327,27 +359,49 @@ DSG_D void load_ring(uint8_t *s_data, const LzParams &P, int64_t cs, int rp0, in
 // round cost 1-3 % of compressed size (tools/lzmodel.cc, SCRAMBLE=512).
 // Positions in the interior of a byte run (the five bytes p-1..p+3 are equal) are not inserted: every one of
 // them would land in the same bucket (quadratic walks, useless candidates); the search gives them the
-// distance-1 candidate directly. Their chain start is whatever the head holds when they look (an entry of the
-// same round that lies ahead of them is skipped by the search).
+// distance-1 candidate directly. Their chain start is the start of their run (second pass of insert_positions):
+// a value that does not depend on how the threads interleave, like everything else here -- the output of the kernel
+// is the same on every run (tools/determinism.py).
 constexpr int kInsRound = kLzThreads;
 constexpr int kInsWalkMax = 96;
+
+// interior of a byte run: the five bytes p-1..p+3 are equal
+DSG_D bool run_interior(const uint8_t *s_data, uint32_t slot, uint32_t v, int rp, int lo_rp) {
+  return rp > lo_rp && v == (v & 0xffu) * 0x01010101u && s_data[slot ? slot - 1 : kRing - 1] == (uint8_t)v;
+}
+
+// A head word holds the slot of the newest position of its bucket in the low half and that position's ring lap in
+// the high half. The lap tells a live entry from one that is a whole lap (or more) old: its slot belongs to a newer
+// position by now, and following it would walk another bucket's chain or a link that is being written at this
+// moment -- a result that depends on timing. Entries in the last kInsRound positions of the lap window are treated
+// as gone too (their slots alias the positions of the running round); they lie beyond kMaxDist anyway.
+DSG_D uint32_t head_word(int rp) { return ring_slot(rp) | ((uint32_t)((rp + kDict) / kRing) << 16); }
+
+// Slot of the entry a head word names, or kNil when the entry is not live as seen from position rp.
+// ahead_ok: positions later in the stream (by less than kInsRound) count as live.
+DSG_D uint32_t head_entry(uint32_t word, int rp, bool ahead_ok) {
+  const uint32_t s = word & 0xffffu;
+  if (s == kNil) return kNil;
+  const int cur = rp + kDict;                                   // ring position index of rp
+  const int ent = (int)(word >> 16) * kRing + (int)s;           // ... of the entry
+  const int delta = cur - ent;                                  // > 0: the entry is older
+  if (delta >= kRing - kInsRound || delta <= (ahead_ok ? -kInsRound : 0)) return kNil;
+  return s;
+}
 
 DSG_D void insert_one(const uint8_t *s_data, unsigned short *prev16, uint32_t *s_head, int rp, int lo_rp) {
   const uint32_t slot = ring_slot(rp);
   const uint32_t v = load4(s_data + slot);
   const uint32_t h = hash4(v);
-  // interior of a byte run: the five bytes p-1..p+3 are equal
-  if (rp > lo_rp && v == (v & 0xffu) * 0x01010101u && s_data[slot ? slot - 1 : kRing - 1] == (uint8_t)v) {
-    prev16[slot] = (unsigned short)s_head[h];
-    return;
-  }
+  if (run_interior(s_data, slot, v, rp, lo_rp)) return;  // gets its chain start in the second pass
+  const uint32_t mine = head_word(rp);
   bool at_head = true;
   uint32_t holder = h;  // the link we would be written into: head[h], or prev[holder]
   int walked = 0;
   for (;;) {
-    const uint32_t nxt = at_head ? s_head[holder] : (uint32_t)prev16[holder];
-    // The bound guards against stale links: a slot of this round that has not been inserted yet still holds the
-    // link of the position that occupied it one ring lap ago, and such links can form cycles.
+    const uint32_t word = at_head ? s_head[holder] : (uint32_t)prev16[holder];
+    const uint32_t nxt = at_head ? head_entry(word, rp, true) : word;
+    // The bound guards against an unexpectedly long stretch of entries of this round in one bucket.
     if (nxt != kNil && ++walked < kInsWalkMax) {
       int fwd = (int)nxt - (int)slot;
       if (fwd < 0) fwd += kRing;
@@ -365,20 +419,49 @@ DSG_D void insert_one(const uint8_t *s_data, unsigned short *prev16, uint32_t *s
 #else
     asm volatile("" ::: "memory");
 #endif
-    const uint32_t seen = at_head ? atomicCAS(&s_head[holder], nxt, slot)
-                                  : (uint32_t)atomicCAS(&prev16[holder], (unsigned short)nxt, (unsigned short)slot);
-    if (seen == nxt) break;  // else somebody linked in first: look at the same link again
+    const uint32_t seen = at_head ? atomicCAS(&s_head[holder], word, mine)
+                                  : (uint32_t)atomicCAS(&prev16[holder], (unsigned short)word, (unsigned short)slot);
+    if (seen == word) break;  // else somebody linked in first: look at the same link again
   }
 }
 
+// `run_start` (shared memory, one word per run of chunks): position + kDict + 1 of the last position before rp0 that
+// is not a run interior, 0 = none; updated to the same for rp1. `scratch`: >= 33 words for the scan.
 DSG_D void insert_positions(const uint8_t *s_data, uint16_t *s_prev, uint32_t *s_head, int rp0, int rp1, int lo_rp,
-                            const LzGroup &g) {
+                            const LzGroup &g, uint32_t *scratch, uint32_t *run_start) {
   unsigned short *prev16 = reinterpret_cast<unsigned short *>(s_prev);
   for (int base = rp0; base < rp1; base += g.n) {  // g.n <= kInsRound positions per round (two per thread: slower)
     const int r0 = base + g.tid;
     if (r0 < rp1) insert_one(s_data, prev16, s_head, r0, lo_rp);
     group_sync(g);  // rounds are ordered
   }
+  // Second pass: every run interior gets the START of its byte run as its chain start -- the nearest position before
+  // it that is not an interior; that position sits in the same bucket (its four bytes are the run byte too), so its
+  // own link leads on to the earlier runs. A running maximum over the range, carried from range to range.
+  const int per = (rp1 - rp0 + g.n - 1) / g.n;
+  const int lo = rp0 + g.tid * per < rp1 ? rp0 + g.tid * per : rp1;
+  const int hi = lo + per < rp1 ? lo + per : rp1;
+  uint32_t last = 0;
+  for (int r = lo; r < hi; r++) {
+    const uint32_t slot = ring_slot(r);
+    if (!run_interior(s_data, slot, load4(s_data + slot), r, lo_rp)) last = (uint32_t)(r + kDict + 1);
+  }
+  uint32_t total;
+  uint32_t cur = group_exclusive_max(last, scratch, &total, g);
+  const uint32_t carry = *run_start;
+  if (cur == 0) cur = carry;
+  for (int r = lo; r < hi; r++) {
+    const uint32_t slot = ring_slot(r);
+    if (run_interior(s_data, slot, load4(s_data + slot), r, lo_rp)) {
+      const int start_rp = (int)cur - kDict - 1;
+      prev16[slot] = (cur != 0 && r - start_rp <= kMaxDist) ? (unsigned short)ring_slot(start_rp) : (unsigned short)kNil;
+    } else {
+      cur = (uint32_t)(r + kDict + 1);
+    }
+  }
+  group_sync(g);  // everybody has read the carry
+  if (g.tid == 0 && total != 0) *run_start = total;
+  group_sync(g);
 }
 
 // Longest match for every position of the tile. tile_rp = run-relative position of the tile start, chunk_end =
@@ -396,7 +479,7 @@ constexpr int kSubRun = kRun / kWays;
 struct SearchWay {
   int j, st, pos0;  // position index inside the sub-run, state, tile-relative first position
   int inh_len, inh_dist;
-  int maxlen, best, bdist, depth, max_back, last_d, skips, cmps;
+  int maxlen, best, bdist, depth, max_back, last_d, cmps;
   int cl, cd;  // compare state: bytes matched so far, distance of the candidate
   uint32_t slot, q, qn, aw, v_prev;
   const uint8_t *a, *cb;
@@ -407,7 +490,7 @@ DSG_D void search_way_init(SearchWay &w, const uint8_t *s_data, int tile_rp, int
   w.st = 0;
   w.pos0 = pos0;
   w.inh_len = w.inh_dist = 0;
-  w.maxlen = w.best = w.bdist = w.depth = w.max_back = w.last_d = w.skips = w.cmps = w.cl = w.cd = 0;
+  w.maxlen = w.best = w.bdist = w.depth = w.max_back = w.last_d = w.cmps = w.cl = w.cd = 0;
   w.slot = ring_slot(tile_rp + pos0);
   w.q = w.qn = kNil;
   w.aw = 0;
@@ -428,7 +511,6 @@ DSG_D void search_way_setup(SearchWay &w, const uint8_t *s_data, const uint16_t 
   w.depth = 0;
   w.q = kNil;
   w.last_d = 0;
-  w.skips = 0;
   w.cmps = 0;
   w.st = kWalk;
   const uint32_t v = load4(w.a);
@@ -479,14 +561,7 @@ DSG_D void search_walk_step(SearchWay &w, const uint8_t *s_data, const uint16_t 
   int d = (int)w.slot - (int)w.q;
   if (d <= 0) d += kRing;
   if (d > w.max_back || d <= w.last_d) {
-    if (d > kRing - kInsRound && w.skips < 64) {
-      // the chain start of a run-interior position may be an entry of its own round that lies ahead
-      w.skips++;
-      w.depth++;
-      w.q = s_prev[w.q];
-    } else {
-      w.q = kNil;  // left the window, or a stale link (chains are in exact stream order: distances grow)
-    }
+    w.q = kNil;  // left the window, or a stale link (chains are in exact stream order: distances grow)
     return;
   }
   w.last_d = d;
@@ -553,7 +628,7 @@ DSG_D void search_tile(const uint8_t *s_data, const uint16_t *s_prev, uint8_t *s
         run = atomicAdd(ctr, 1u);
         if (run >= nruns) break;
         search_way_init(w, s_data, tile_rp, (int)run * kSearchRun, lo_rp);
-        search_way_setup(w, s_data, s_prev, tile_rp, chunk_end, lo_rp);
+              search_way_setup(w, s_data, s_prev, tile_rp, chunk_end, lo_rp);
       }
     }
   }
@@ -623,7 +698,8 @@ DSG_D uint32_t refine_build_list(const uint8_t *s_mlen, const uint16_t *s_mdist,
 constexpr int kChase = 4;
 
 DSG_D void refine_search(const uint8_t *s_data, const uint16_t *s_prev, uint8_t *s_mlen, uint16_t *s_mdist,
-                         const uint16_t *s_work, uint32_t nwork, int tile_rp, int chunk_end, int lo_rp, uint32_t *ctr) {
+                         const uint16_t *s_work, uint32_t nwork, int tile_rp, int tile_len, int chunk_end, int lo_rp,
+                         uint32_t *ctr) {
   const SmemBase sd = smem_base(s_data), sp = smem_base(s_prev);
   for (;;) {
     const uint32_t k = atomicAdd(ctr, 1u);
@@ -666,10 +742,8 @@ DSG_D void refine_search(const uint8_t *s_data, const uint16_t *s_prev, uint8_t 
             if (d <= 0) d += kRing;
             depth--;
             if (d > max_back || d <= last_d) {
-              if (d <= kRing - kInsRound) {  // left the window, or a stale link
-                stop = true;
-                nq = kNil;
-              }                              // else: an entry of the same insertion round that lies ahead: skip it
+              stop = true;  // left the window, or a stale link (chains are in exact stream order: distances grow)
+              nq = kNil;
             } else {
               last_d = d;
               if (f[i] == want) {
@@ -1012,7 +1086,9 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
     const LzGroup g_all{(int)tid, kLzThreads, 0};
     load_ring(s_data, P, rs, -(((-lo_rp) + 15) & ~15), kTile + kLook, g_all);
     __syncthreads();
-    insert_positions(s_data, s_prev, s_head, lo_rp, 0, lo_rp, g_all);
+    if (tid == 0) s_misc[kMRunStart] = 0;
+    __syncthreads();
+    insert_positions(s_data, s_prev, s_head, lo_rp, 0, lo_rp, g_all, s_misc + kMScan, &s_misc[kMRunStart]);
     LZ_PROF(kProfLoad);
 
     for (uint32_t k = 0; k < rlen; k++) {
@@ -1051,7 +1127,8 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
         group_sync(g_team);
       }
       LZ_PROF(kProfLoad);
-      insert_positions(s_data, s_prev, s_head, tile_rp, tile_rp + tile_len, lo_rp, g_team);  // ends with a barrier
+      insert_positions(s_data, s_prev, s_head, tile_rp, tile_rp + tile_len, lo_rp, g_team, t_scan,
+                       &s_misc[kMRunStart]);  // ends with a barrier
       if (has_next) handoff_arrive(kBarInsert + (int)team);
       LZ_PROF(kProfInsert);
       if (g_team.tid == 0) *t_ctr = 0;
@@ -1074,7 +1151,7 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
         const uint32_t nwork = refine_build_list(t_mlen, t_mdist, t_bitmap, t_deep, t_work, t_scan, tile_len, g_team);
         LZ_PROF(kProfRefList);
         const long long t_wd = P.prof ? clock64() : 0;
-        refine_search(s_data, s_prev, t_mlen, t_mdist, t_work, nwork, tile_rp, crp + chunk_len, lo_rp, t_ctr);
+        refine_search(s_data, s_prev, t_mlen, t_mdist, t_work, nwork, tile_rp, tile_len, crp + chunk_len, lo_rp, t_ctr);
         if (P.prof && team == 0 && lane == 0)
           atomicAdd(&P.prof[kProfWarpDeep], (unsigned long long)(clock64() - t_wd) / kTeamWarps);
         group_sync(g_team);
