@@ -252,3 +252,18 @@ def test_pack_to_fd_streams_the_same_bytes(tmp_path, tar_only):
             signal.signal(signal.SIGPIPE, old)
             os.close(w)
         assert gzip.decompress(p.pack(man)) == ref  # the context is still usable
+
+
+def test_level6_output_is_deterministic_and_equals_the_emulator(packer6):
+    """Same input, same bytes: run to run on the GPU, and GPU against the same kernel source under the CPU emulator
+    (so the emulator tests of the CPU suite speak for the GPU build)."""
+    from devspace_b200 import synth
+    from test_emu_deflate import emu_deflate
+    data = (synth.text_like(90_000, 31).numpy().tobytes() + b"\0" * 5000 + synth.binary_like(80_000, 32).numpy().tobytes()
+            + synth.random_bytes(20_000, 33).numpy().tobytes())
+    a = packer6.deflate(data, level=6)
+    assert a == packer6.deflate(data, level=6)
+    assert zlib.decompress(a, -15) == data
+    assert a == emu_deflate(data, grid=2, run_chunks=1)
+    big = synth.binary_like(8_000_000, 34).numpy().tobytes()
+    assert packer6.deflate(big, level=6) == packer6.deflate(big, level=6)
