@@ -56,7 +56,7 @@ constexpr int kHashBits = 13;
 constexpr int kHashSize = 1 << kHashBits;
 constexpr int kMinMatch = 4;
 constexpr int kMaxMatch = 258;
-constexpr int kDepth = 6;          // first pass: every position, shallow
+constexpr int kDepth = 2;          // first pass: every position, shallow
 constexpr int kDeepDepth = 160;    // second pass: token starts and their lazy successors only
 constexpr int kRefineRounds = 2;
 constexpr int kMaxCompares = 16;   // full compares per position
