@@ -68,8 +68,12 @@ constexpr int kStageBytes = 16384;        // bit-packing window
 constexpr int kBatchTokens = 2048;        // tokens per bit-packing batch (<= 48 bits each = 12 KiB)
 constexpr int kTokPerThread = kBatchTokens / kLzThreads;
 constexpr uint32_t kTokMatch = 0x80000000u;
-constexpr int kTokSlotWords = kChunk + 64;  // per-CTA token scratch (u32), worst case all literals + EOB
-constexpr int kSlotBytes = kChunk + 128;    // per-chunk output slot in the scratch buffer (16-byte aligned)
+// kChunk is the unit; a launch may use chunks of 1, 2 or 4 units (LzParams::chunk_bytes): a chunk is one deflate
+// block with one pair of Huffman tables, and its epilogue (tree construction, sizes, bit packing, the drain of the
+// tile pipeline) is the part of the kernel in which most threads wait -- large inputs amortise it over more bytes.
+constexpr int kMaxChunk = 4 * kChunk;
+constexpr int kTokSlotWords = kMaxChunk + 64;  // per-CTA token scratch (u32), worst case all literals + EOB
+DSG_HD uint32_t lz_slot_bytes(uint32_t chunk_bytes) { return chunk_bytes + 128; }  // per-chunk output slot (16-byte aligned)
 
 // Upper bound of the raw deflate output for n input bytes: a chunk never exceeds its stored encoding
 // (two stored blocks for a 64 KiB chunk), plus the 2-byte terminator.
@@ -117,7 +121,8 @@ struct LzParams {
   uint64_t len;               // bytes
   const uint8_t *dict;        // up to 32 KiB that precede `in` in the member (previous segment), or null
   uint32_t dict_len;
-  uint8_t *slots;             // per-chunk output slots, kSlotBytes apart (scratch)
+  uint32_t chunk_bytes;       // kChunk, 2 * kChunk or kMaxChunk
+  uint8_t *slots;             // per-chunk output slots, lz_slot_bytes(chunk_bytes) apart (scratch)
   uint32_t *chunk_meta;       // per chunk: (bytes << 1) | stored flag (scratch)
   uint32_t nchunks;
   uint32_t run_chunks;        // consecutive chunks one ticket hands out (the LZ window slides across them)
@@ -1077,7 +1082,8 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
     // chains and the ring carry over from chunk to chunk, only the first chunk has to hash its dictionary.
     const uint32_t c0 = run < nbig ? run * R : nbig * R + (run - nbig);
     const uint32_t rlen = run < nbig ? R : 1u;
-    const int64_t rs = (int64_t)c0 * kChunk;  // stream offset of the run
+    const int chunk = (int)P.chunk_bytes;
+    const int64_t rs = (int64_t)c0 * chunk;  // stream offset of the run
     const int64_t avail = rs + (P.dict ? (int64_t)P.dict_len : 0);
     const int lo_rp = -(int)(avail < (int64_t)kMaxDist ? avail : (int64_t)kMaxDist);
     for (uint32_t i = tid; i < (uint32_t)kHashSize; i += kLzThreads) s_head[i] = kNil;
@@ -1094,9 +1100,9 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
     for (uint32_t k = 0; k < rlen; k++) {
     const uint32_t c = c0 + k;
     if (c >= P.nchunks) break;
-    const int64_t cs = (int64_t)c * kChunk;
-    const int crp = (int)(k * kChunk);  // run-relative position of the chunk start
-    const int chunk_len = (int)((int64_t)P.len - cs < kChunk ? (int64_t)P.len - cs : kChunk);
+    const int64_t cs = (int64_t)c * chunk;
+    const int crp = (int)k * chunk;  // run-relative position of the chunk start
+    const int chunk_len = (int)((int64_t)P.len - cs < chunk ? (int64_t)P.len - cs : chunk);
     __syncthreads();
     for (uint32_t i = tid; i < 288; i += kLzThreads) s_lfreq[i] = 0;
     if (tid < 32) s_dfreq[tid] = 0;
@@ -1295,7 +1301,7 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
     LZ_PROF(kProfSizes);
     const uint32_t mode = s_misc[kMMode];
     const uint32_t chunk_bytes = s_misc[kMChunkBytes];
-    uint8_t *dst = P.slots + (size_t)c * kSlotBytes;
+    uint8_t *dst = P.slots + (size_t)c * lz_slot_bytes(P.chunk_bytes);
 
     if (mode == 0) {
       // stored: the gather kernel copies the bytes straight from the input
@@ -1396,13 +1402,11 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
         const uint32_t whole = bitpos / 8 - flushed;
         const bool last = b0 + kBatchTokens >= ntok;
         if (!last) {
+          // every thread reads the partial byte itself; only the words this batch touched are cleared again
+          const uint32_t carry = (bitpos & 7) ? reinterpret_cast<const uint8_t *>(s_stage)[whole] : 0u;
           block_copy_unaligned(dst + flushed, reinterpret_cast<const uint8_t *>(s_stage), whole, tid, kLzThreads);
           __syncthreads();
-          const uint32_t carry = reinterpret_cast<const uint8_t *>(s_stage)[whole];
-          __syncthreads();
-          for (uint32_t i = tid; i < (uint32_t)kStageBytes / 4; i += kLzThreads) s_stage[i] = 0;
-          __syncthreads();
-          if (tid == 0) s_stage[0] = (bitpos & 7) ? carry : 0;
+          for (uint32_t i = tid; i < whole / 4 + 2; i += kLzThreads) s_stage[i] = i == 0 ? carry : 0u;
           flushed += whole;
           __syncthreads();
         } else {
@@ -1478,15 +1482,16 @@ __global__ void __launch_bounds__(1024) lz_scan_kernel(const uint32_t *__restric
 __global__ void __launch_bounds__(256)
 lz_gather_kernel(const uint8_t *__restrict__ in, uint64_t len, const uint8_t *__restrict__ slots,
                  const uint32_t *__restrict__ chunk_meta, const uint64_t *__restrict__ offs, uint32_t nchunks,
-                 uint8_t *__restrict__ out, int write_terminator, const uint32_t *__restrict__ error) {
+                 uint32_t chunk_bytes, uint8_t *__restrict__ out, int write_terminator,
+                 const uint32_t *__restrict__ error) {
   if (*error) return;  // output too small: nothing is written
   const uint32_t c = blockIdx.x;
   const uint32_t meta = chunk_meta[c];
   const uint32_t bytes = meta >> 1;
   uint8_t *dst = out + offs[c];
   if (meta & 1u) {
-    const uint64_t cs = (uint64_t)c * kChunk;
-    const uint32_t chunk_len = (uint32_t)(len - cs < (uint64_t)kChunk ? len - cs : (uint64_t)kChunk);
+    const uint64_t cs = (uint64_t)c * chunk_bytes;
+    const uint32_t chunk_len = (uint32_t)(len - cs < (uint64_t)chunk_bytes ? len - cs : (uint64_t)chunk_bytes);
     uint32_t done = 0, o = 0;
     while (done < chunk_len) {
       const uint32_t n = chunk_len - done < kStoredMax ? chunk_len - done : kStoredMax;
@@ -1502,7 +1507,7 @@ lz_gather_kernel(const uint8_t *__restrict__ in, uint64_t len, const uint8_t *__
       o += n + 5;
     }
   } else {
-    block_copy_unaligned(dst, slots + (size_t)c * kSlotBytes, bytes, threadIdx.x, 256);
+    block_copy_unaligned(dst, slots + (size_t)c * lz_slot_bytes(chunk_bytes), bytes, threadIdx.x, 256);
   }
   if (write_terminator && c == nchunks - 1 && threadIdx.x == 0) {
     dst[bytes] = 0x03;  // BFINAL=1, BTYPE=01, end-of-block

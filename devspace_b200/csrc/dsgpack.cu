@@ -327,7 +327,14 @@ int lz_launch(dsg_ctx *ctx, cudaStream_t stream, const uint8_t *d_in, uint64_t l
     LAUNCH_CHECK();
     return DSG_OK;
   }
-  const uint64_t nchunks64 = (len + kChunk - 1) / kChunk;
+  // Chunk size: the largest of 64 / 128 / 256 KiB that still leaves every SM eight chunks (see kMaxChunk).
+  uint32_t chunk_bytes = kChunk;
+  while (chunk_bytes < (uint32_t)kMaxChunk && len / (2ull * chunk_bytes) >= 8ull * (uint64_t)ctx->sm_count) chunk_bytes *= 2;
+  if (const char *g = getenv("DSG_LZ_CHUNK")) {  // development aid: 1, 2 or 4 units of 64 KiB
+    const long v = strtol(g, nullptr, 10);
+    if (v == 1 || v == 2 || v == 4) chunk_bytes = (uint32_t)v * kChunk;
+  }
+  const uint64_t nchunks64 = (len + chunk_bytes - 1) / chunk_bytes;
   if (nchunks64 > 0xfffffff0ull) return fail(ctx, DSG_E_ARG, "input too large for one call");
   const uint32_t nchunks = (uint32_t)nchunks64;
   // chunks per run: long runs amortise hashing the dictionary, short ones keep every SM busy on small inputs
@@ -348,7 +355,7 @@ int lz_launch(dsg_ctx *ctx, cudaStream_t stream, const uint8_t *d_in, uint64_t l
   // scratch: per-chunk output slots + sizes + offsets, the ticket word, token slots (one per resident CTA)
   const size_t meta_bytes = (sizeof(uint64_t) + sizeof(uint32_t)) * (size_t)nchunks + 64;
   CU(ctx->chunk_sizes.ensure(meta_bytes));
-  CU(ctx->chunk_slots.ensure((size_t)kSlotBytes * nchunks));
+  CU(ctx->chunk_slots.ensure((size_t)lz_slot_bytes(chunk_bytes) * nchunks));
   CU(ctx->lz_scratch.ensure(sizeof(uint32_t) * (size_t)kTokSlotWords * ctx->sm_count));
   uint64_t *offs = ctx->chunk_sizes.as<uint64_t>();
   uint32_t *meta = reinterpret_cast<uint32_t *>(offs + nchunks);
@@ -359,6 +366,7 @@ int lz_launch(dsg_ctx *ctx, cudaStream_t stream, const uint8_t *d_in, uint64_t l
   P.len = len;
   P.dict = dict_len ? d_dict : nullptr;
   P.dict_len = dict_len;
+  P.chunk_bytes = chunk_bytes;
   P.slots = ctx->chunk_slots.as<uint8_t>();
   P.chunk_meta = meta;
   P.nchunks = nchunks;
@@ -377,7 +385,8 @@ int lz_launch(dsg_ctx *ctx, cudaStream_t stream, const uint8_t *d_in, uint64_t l
   LAUNCH_CHECK();
   lz_scan_kernel<<<1, 1024, 0, stream>>>(meta, nchunks, offs, out_cap, write_terminator, d_total, d_error);
   LAUNCH_CHECK();
-  lz_gather_kernel<<<nchunks, 256, 0, stream>>>(d_in, len, P.slots, meta, offs, nchunks, d_out, write_terminator, d_error);
+  lz_gather_kernel<<<nchunks, 256, 0, stream>>>(d_in, len, P.slots, meta, offs, nchunks, chunk_bytes, d_out,
+                                                write_terminator, d_error);
   LAUNCH_CHECK();
   if (prof_on) {
     unsigned long long h[kProfSlots];
@@ -1054,7 +1063,7 @@ static int pack_host_pipelined(dsg_ctx *ctx, const dsg_entry *entries, size_t n,
   if (gzip && ctx->opts.level != DSG_LEVEL_STORED) {
     const uint64_t nch = (std::min(S, T) + kChunk - 1) / kChunk;
     CU(ctx->chunk_sizes.ensure((sizeof(uint64_t) + sizeof(uint32_t)) * (size_t)nch + 64));
-    CU(ctx->chunk_slots.ensure((size_t)kSlotBytes * nch));
+    CU(ctx->chunk_slots.ensure((size_t)lz_slot_bytes(kChunk) * nch));  // covers every chunk size: fewer, larger slots
     CU(ctx->lz_scratch.ensure(sizeof(uint32_t) * (size_t)kTokSlotWords * ctx->sm_count));
   }
   if (gzip) {

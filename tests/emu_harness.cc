@@ -69,12 +69,17 @@ int emu_lz_deflate(const uint8_t *in, uint64_t len, const uint8_t *dict, uint32_
     *out_len = 2;
     return 0;
   }
-  const uint32_t nchunks = (uint32_t)((len + kChunk - 1) / kChunk);
+  // bits 16.. of run_chunks: chunk size in units of 64 KiB (0 = 1), as the host picks it for large inputs
+  uint32_t units = run_chunks >> 16;
+  run_chunks &= 0xffffu;
+  if (units != 2 && units != 4) units = 1;
+  const uint32_t chunk_bytes = units * (uint32_t)kChunk;
+  const uint32_t nchunks = (uint32_t)((len + chunk_bytes - 1) / chunk_bytes);
   if (run_chunks == 0) run_chunks = 1;
   const uint32_t big_runs = nchunks / run_chunks;  // the remainder goes chunk by chunk (the tail tickets)
   const uint32_t nruns = big_runs + (nchunks - big_runs * run_chunks);
   if (grid == 0 || grid > nruns) grid = nruns;
-  std::vector<uint8_t> slots((size_t)nchunks * kSlotBytes, 0xAB);
+  std::vector<uint8_t> slots((size_t)nchunks * lz_slot_bytes(chunk_bytes), 0xAB);
   std::vector<uint32_t> meta(nchunks, 0);
   std::vector<uint64_t> offs(nchunks, 0);
   std::vector<uint32_t> tok((size_t)grid * kTokSlotWords, 0xDEADBEEF);
@@ -85,6 +90,7 @@ int emu_lz_deflate(const uint8_t *in, uint64_t len, const uint8_t *dict, uint32_
   P.len = len;
   P.dict = dict;
   P.dict_len = dict_len;
+  P.chunk_bytes = chunk_bytes;
   P.slots = slots.data();
   P.chunk_meta = meta.data();
   P.nchunks = nchunks;
@@ -96,7 +102,7 @@ int emu_lz_deflate(const uint8_t *in, uint64_t len, const uint8_t *dict, uint32_
   emu::launch(dim3(grid), dim3(kLzThreads), LzLayout::total, [&] { lz_deflate_kernel(P); });
   emu::launch(dim3(1), dim3(1024), 0, [&] { lz_scan_kernel(meta.data(), nchunks, offs.data(), cap, 1, &total, &error); });
   emu::launch(dim3(nchunks), dim3(256), 0, [&] {
-    lz_gather_kernel(in, len, slots.data(), meta.data(), offs.data(), nchunks, out, 1, &error);
+    lz_gather_kernel(in, len, slots.data(), meta.data(), offs.data(), nchunks, chunk_bytes, out, 1, &error);
   });
   *out_len = total;
   return error ? DSG_E_CAPACITY : 0;

@@ -21,7 +21,7 @@ def _lib():
     return lib
 
 
-def emu_deflate(data: bytes, grid: int = 0, dict_: bytes = b"", run_chunks: int = 1):
+def emu_deflate(data: bytes, grid: int = 0, dict_: bytes = b"", run_chunks: int = 1, chunk_units: int = 1):
     L = _lib()
     a = np.frombuffer(data, np.uint8)
     d = np.frombuffer(dict_, np.uint8)
@@ -31,7 +31,7 @@ def emu_deflate(data: bytes, grid: int = 0, dict_: bytes = b"", run_chunks: int 
     rc = L.emu_lz_deflate(ctypes.c_void_p(a.ctypes.data if len(data) else None), ctypes.c_uint64(len(data)),
                           ctypes.c_void_p(d.ctypes.data if len(dict_) else None), ctypes.c_uint32(len(dict_)),
                           ctypes.c_void_p(out.ctypes.data), ctypes.c_uint64(cap), ctypes.byref(n), ctypes.c_uint32(grid),
-                          ctypes.c_uint32(run_chunks))
+                          ctypes.c_uint32(run_chunks | (chunk_units << 16)))
     assert rc == 0
     return out[: n.value].tobytes()
 

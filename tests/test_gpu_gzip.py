@@ -267,3 +267,18 @@ def test_level6_output_is_deterministic_and_equals_the_emulator(packer6):
     assert a == emu_deflate(data, grid=2, run_chunks=1)
     big = synth.binary_like(8_000_000, 34).numpy().tobytes()
     assert packer6.deflate(big, level=6) == packer6.deflate(big, level=6)
+
+
+@pytest.mark.parametrize("units", [2, 4])
+def test_level6_large_chunks(packer6, units, monkeypatch):
+    """Inputs of hundreds of MB are cut into 128 / 256 KiB chunks (one deflate block each); DSG_LZ_CHUNK forces that
+    on a small input: the stream must inflate, stay within the size bound, and equal the emulator's bytes."""
+    from devspace_b200 import synth
+    from test_emu_deflate import emu_deflate
+    monkeypatch.setenv("DSG_LZ_CHUNK", str(units))
+    data = synth.text_like(3_000_000, 41).numpy().tobytes() + synth.binary_like(2_000_001, 42).numpy().tobytes()
+    raw = packer6.deflate(data, level=6)
+    assert zlib.decompress(raw, -15) == data
+    assert len(raw) <= 1.03 * _zlib6(data)
+    small = data[2_900_000:3_300_000]                      # text, then binary: 400 000 bytes, a short last chunk
+    assert packer6.deflate(small, level=6) == emu_deflate(small, grid=2, run_chunks=1, chunk_units=units)
