@@ -74,6 +74,15 @@ constexpr uint32_t kTokMatch = 0x80000000u;
 constexpr int kMaxChunk = 4 * kChunk;
 constexpr int kTokSlotWords = kMaxChunk + 64;  // per-CTA token scratch (u32), worst case all literals + EOB
 DSG_HD uint32_t lz_slot_bytes(uint32_t chunk_bytes) { return chunk_bytes + 128; }  // per-chunk output slot (16-byte aligned)
+// The first big_chunks chunks of a launch have chunk_bytes bytes (they are handed out in runs), the chunks behind
+// them kChunk bytes (handed out one by one at the end of the launch, where a big chunk would leave SMs idle for long).
+DSG_HD uint64_t lz_chunk_offset(uint32_t c, uint32_t chunk_bytes, uint32_t big_chunks) {
+  return c < big_chunks ? (uint64_t)c * chunk_bytes
+                        : (uint64_t)big_chunks * chunk_bytes + (uint64_t)(c - big_chunks) * (uint64_t)kChunk;
+}
+DSG_HD uint32_t lz_chunk_size(uint32_t c, uint32_t chunk_bytes, uint32_t big_chunks) {
+  return c < big_chunks ? chunk_bytes : (uint32_t)kChunk;
+}
 
 // Upper bound of the raw deflate output for n input bytes: a chunk never exceeds its stored encoding
 // (two stored blocks for a 64 KiB chunk), plus the 2-byte terminator.
@@ -1082,8 +1091,8 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
     // chains and the ring carry over from chunk to chunk, only the first chunk has to hash its dictionary.
     const uint32_t c0 = run < nbig ? run * R : nbig * R + (run - nbig);
     const uint32_t rlen = run < nbig ? R : 1u;
-    const int chunk = (int)P.chunk_bytes;
-    const int64_t rs = (int64_t)c0 * chunk;  // stream offset of the run
+    const int chunk = (int)lz_chunk_size(c0, P.chunk_bytes, nbig * R);  // a run has chunks of one size
+    const int64_t rs = (int64_t)lz_chunk_offset(c0, P.chunk_bytes, nbig * R);  // stream offset of the run
     const int64_t avail = rs + (P.dict ? (int64_t)P.dict_len : 0);
     const int lo_rp = -(int)(avail < (int64_t)kMaxDist ? avail : (int64_t)kMaxDist);
     for (uint32_t i = tid; i < (uint32_t)kHashSize; i += kLzThreads) s_head[i] = kNil;
@@ -1100,7 +1109,7 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
     for (uint32_t k = 0; k < rlen; k++) {
     const uint32_t c = c0 + k;
     if (c >= P.nchunks) break;
-    const int64_t cs = (int64_t)c * chunk;
+    const int64_t cs = rs + (int64_t)k * chunk;
     const int crp = (int)k * chunk;  // run-relative position of the chunk start
     const int chunk_len = (int)((int64_t)P.len - cs < chunk ? (int64_t)P.len - cs : chunk);
     __syncthreads();
@@ -1482,7 +1491,7 @@ __global__ void __launch_bounds__(1024) lz_scan_kernel(const uint32_t *__restric
 __global__ void __launch_bounds__(256)
 lz_gather_kernel(const uint8_t *__restrict__ in, uint64_t len, const uint8_t *__restrict__ slots,
                  const uint32_t *__restrict__ chunk_meta, const uint64_t *__restrict__ offs, uint32_t nchunks,
-                 uint32_t chunk_bytes, uint8_t *__restrict__ out, int write_terminator,
+                 uint32_t chunk_bytes, uint32_t big_chunks, uint8_t *__restrict__ out, int write_terminator,
                  const uint32_t *__restrict__ error) {
   if (*error) return;  // output too small: nothing is written
   const uint32_t c = blockIdx.x;
@@ -1490,8 +1499,9 @@ lz_gather_kernel(const uint8_t *__restrict__ in, uint64_t len, const uint8_t *__
   const uint32_t bytes = meta >> 1;
   uint8_t *dst = out + offs[c];
   if (meta & 1u) {
-    const uint64_t cs = (uint64_t)c * chunk_bytes;
-    const uint32_t chunk_len = (uint32_t)(len - cs < (uint64_t)chunk_bytes ? len - cs : (uint64_t)chunk_bytes);
+    const uint64_t cs = lz_chunk_offset(c, chunk_bytes, big_chunks);
+    const uint64_t csz = lz_chunk_size(c, chunk_bytes, big_chunks);
+    const uint32_t chunk_len = (uint32_t)(len - cs < csz ? len - cs : csz);
     uint32_t done = 0, o = 0;
     while (done < chunk_len) {
       const uint32_t n = chunk_len - done < kStoredMax ? chunk_len - done : kStoredMax;

@@ -321,6 +321,9 @@ __global__ void lz_finish_empty_kernel(uint8_t *out, uint64_t *total_out, int wr
 int lz_launch(dsg_ctx *ctx, cudaStream_t stream, const uint8_t *d_in, uint64_t len, const uint8_t *d_dict,
               uint32_t dict_len, uint8_t *d_out, uint64_t out_cap, uint64_t *d_total, uint32_t *d_error,
               int write_terminator) {
+  DevBuf &b_sizes = ctx->chunk_sizes;
+  DevBuf &b_slots = ctx->chunk_slots;
+  DevBuf &b_tok = ctx->lz_scratch;
   if (len == 0) {
     if (out_cap < 2 && write_terminator) return fail(ctx, DSG_E_CAPACITY, "deflate output needs 2 bytes");
     lz_finish_empty_kernel<<<1, 32, 0, stream>>>(d_out, d_total, write_terminator);
@@ -334,19 +337,24 @@ int lz_launch(dsg_ctx *ctx, cudaStream_t stream, const uint8_t *d_in, uint64_t l
     const long v = strtol(g, nullptr, 10);
     if (v == 1 || v == 2 || v == 4) chunk_bytes = (uint32_t)v * kChunk;
   }
-  const uint64_t nchunks64 = (len + chunk_bytes - 1) / chunk_bytes;
-  if (nchunks64 > 0xfffffff0ull) return fail(ctx, DSG_E_ARG, "input too large for one call");
-  const uint32_t nchunks = (uint32_t)nchunks64;
-  // chunks per run: long runs amortise hashing the dictionary, short ones keep every SM busy on small inputs
-  uint32_t run_chunks = std::max<uint32_t>(1, std::min<uint32_t>(8, nchunks / (4 * (uint32_t)ctx->sm_count)));
+  // Runs of run_chunks big chunks first (long runs amortise hashing the dictionary); the last half run per SM is cut
+  // into 64 KiB chunks and handed out one by one, so that the CTAs finish within a millisecond of each other.
+  const uint64_t big_total = (len + chunk_bytes - 1) / chunk_bytes;
+  uint32_t run_chunks = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(8, big_total / (4 * (uint64_t)ctx->sm_count)));
   if (const char *g = getenv("DSG_LZ_RUN")) {
     const long v = strtol(g, nullptr, 10);
     if (v > 0 && v <= 64) run_chunks = (uint32_t)v;
   }
-  // the last (SMs x run_chunks / 2) chunks are handed out one by one: see the ticket comment in lz_deflate_kernel
-  const uint32_t tail = run_chunks > 1 ? std::min<uint32_t>(nchunks, (uint32_t)ctx->sm_count * run_chunks / 2) : nchunks;
-  const uint32_t big_runs = (nchunks - tail) / run_chunks;
-  const uint32_t nruns = big_runs + (nchunks - big_runs * run_chunks);
+  uint64_t tail_bytes = run_chunks > 1 || chunk_bytes > (uint32_t)kChunk
+                            ? std::min<uint64_t>(len, (uint64_t)ctx->sm_count * run_chunks * chunk_bytes / 2)
+                            : len;
+  if (const char *g = getenv("DSG_LZ_TAIL")) tail_bytes = std::min<uint64_t>(len, strtoull(g, nullptr, 10));  // tests
+  const uint64_t big_runs64 = (len - tail_bytes) / ((uint64_t)run_chunks * chunk_bytes);
+  const uint64_t big_chunks64 = big_runs64 * run_chunks;
+  const uint64_t nchunks64 = big_chunks64 + (len - big_chunks64 * chunk_bytes + kChunk - 1) / kChunk;
+  if (nchunks64 > 0xfffffff0ull) return fail(ctx, DSG_E_ARG, "input too large for one call");
+  const uint32_t nchunks = (uint32_t)nchunks64, big_runs = (uint32_t)big_runs64, big_chunks = (uint32_t)big_chunks64;
+  const uint32_t nruns = big_runs + (nchunks - big_chunks);
   uint32_t grid = std::min<uint32_t>(nruns, (uint32_t)ctx->sm_count);
   if (const char *g = getenv("DSG_LZ_GRID")) {  // debugging aid: fewer CTAs => more chunks per CTA
     const long v = strtol(g, nullptr, 10);
@@ -354,10 +362,10 @@ int lz_launch(dsg_ctx *ctx, cudaStream_t stream, const uint8_t *d_in, uint64_t l
   }
   // scratch: per-chunk output slots + sizes + offsets, the ticket word, token slots (one per resident CTA)
   const size_t meta_bytes = (sizeof(uint64_t) + sizeof(uint32_t)) * (size_t)nchunks + 64;
-  CU(ctx->chunk_sizes.ensure(meta_bytes));
-  CU(ctx->chunk_slots.ensure((size_t)lz_slot_bytes(chunk_bytes) * nchunks));
-  CU(ctx->lz_scratch.ensure(sizeof(uint32_t) * (size_t)kTokSlotWords * ctx->sm_count));
-  uint64_t *offs = ctx->chunk_sizes.as<uint64_t>();
+  CU(b_sizes.ensure(meta_bytes));
+  CU(b_slots.ensure((size_t)lz_slot_bytes(chunk_bytes) * nchunks));
+  CU(b_tok.ensure(sizeof(uint32_t) * (size_t)kTokSlotWords * ctx->sm_count));
+  uint64_t *offs = b_sizes.as<uint64_t>();
   uint32_t *meta = reinterpret_cast<uint32_t *>(offs + nchunks);
   uint32_t *ticket = meta + nchunks;
   CU(cudaMemsetAsync(ticket, 0, sizeof(uint32_t), stream));
@@ -367,13 +375,13 @@ int lz_launch(dsg_ctx *ctx, cudaStream_t stream, const uint8_t *d_in, uint64_t l
   P.dict = dict_len ? d_dict : nullptr;
   P.dict_len = dict_len;
   P.chunk_bytes = chunk_bytes;
-  P.slots = ctx->chunk_slots.as<uint8_t>();
+  P.slots = b_slots.as<uint8_t>();
   P.chunk_meta = meta;
   P.nchunks = nchunks;
   P.run_chunks = run_chunks;
   P.big_runs = big_runs;
   P.ticket = ticket;
-  P.tok_scratch = ctx->lz_scratch.as<uint32_t>();
+  P.tok_scratch = b_tok.as<uint32_t>();
   P.prof = nullptr;
   static const bool prof_on = getenv("DSG_LZ_PROF") != nullptr;  // development aid: per-phase cycle counts on stderr
   if (prof_on) {
@@ -385,8 +393,8 @@ int lz_launch(dsg_ctx *ctx, cudaStream_t stream, const uint8_t *d_in, uint64_t l
   LAUNCH_CHECK();
   lz_scan_kernel<<<1, 1024, 0, stream>>>(meta, nchunks, offs, out_cap, write_terminator, d_total, d_error);
   LAUNCH_CHECK();
-  lz_gather_kernel<<<nchunks, 256, 0, stream>>>(d_in, len, P.slots, meta, offs, nchunks, chunk_bytes, d_out,
-                                                write_terminator, d_error);
+  lz_gather_kernel<<<nchunks, 256, 0, stream>>>(d_in, len, P.slots, meta, offs, nchunks, chunk_bytes, big_chunks,
+                                                d_out, write_terminator, d_error);
   LAUNCH_CHECK();
   if (prof_on) {
     unsigned long long h[kProfSlots];

@@ -74,10 +74,12 @@ int emu_lz_deflate(const uint8_t *in, uint64_t len, const uint8_t *dict, uint32_
   run_chunks &= 0xffffu;
   if (units != 2 && units != 4) units = 1;
   const uint32_t chunk_bytes = units * (uint32_t)kChunk;
-  const uint32_t nchunks = (uint32_t)((len + chunk_bytes - 1) / chunk_bytes);
   if (run_chunks == 0) run_chunks = 1;
-  const uint32_t big_runs = nchunks / run_chunks;  // the remainder goes chunk by chunk (the tail tickets)
-  const uint32_t nruns = big_runs + (nchunks - big_runs * run_chunks);
+  // as many whole runs of big chunks as fit, the remainder in 64 KiB chunks one by one (the host's DSG_LZ_TAIL=0)
+  const uint32_t big_runs = (uint32_t)(len / ((uint64_t)run_chunks * chunk_bytes));
+  const uint32_t big_chunks = big_runs * run_chunks;
+  const uint32_t nchunks = big_chunks + (uint32_t)((len - (uint64_t)big_chunks * chunk_bytes + kChunk - 1) / kChunk);
+  const uint32_t nruns = big_runs + (nchunks - big_chunks);
   if (grid == 0 || grid > nruns) grid = nruns;
   std::vector<uint8_t> slots((size_t)nchunks * lz_slot_bytes(chunk_bytes), 0xAB);
   std::vector<uint32_t> meta(nchunks, 0);
@@ -102,7 +104,7 @@ int emu_lz_deflate(const uint8_t *in, uint64_t len, const uint8_t *dict, uint32_
   emu::launch(dim3(grid), dim3(kLzThreads), LzLayout::total, [&] { lz_deflate_kernel(P); });
   emu::launch(dim3(1), dim3(1024), 0, [&] { lz_scan_kernel(meta.data(), nchunks, offs.data(), cap, 1, &total, &error); });
   emu::launch(dim3(nchunks), dim3(256), 0, [&] {
-    lz_gather_kernel(in, len, slots.data(), meta.data(), offs.data(), nchunks, chunk_bytes, out, 1, &error);
+    lz_gather_kernel(in, len, slots.data(), meta.data(), offs.data(), nchunks, chunk_bytes, big_chunks, out, 1, &error);
   });
   *out_len = total;
   return error ? DSG_E_CAPACITY : 0;

@@ -271,11 +271,12 @@ def test_level6_output_is_deterministic_and_equals_the_emulator(packer6):
 
 @pytest.mark.parametrize("units", [2, 4])
 def test_level6_large_chunks(packer6, units, monkeypatch):
-    """Inputs of hundreds of MB are cut into 128 / 256 KiB chunks (one deflate block each); DSG_LZ_CHUNK forces that
-    on a small input: the stream must inflate, stay within the size bound, and equal the emulator's bytes."""
+    """Inputs of hundreds of MB are cut into 128 / 256 KiB chunks (one deflate block each) with 64 KiB chunks at the
+    end of the launch; DSG_LZ_CHUNK / DSG_LZ_TAIL force that on a small input: the stream must inflate, stay within the size bound, and equal the emulator's bytes."""
     from devspace_b200 import synth
     from test_emu_deflate import emu_deflate
     monkeypatch.setenv("DSG_LZ_CHUNK", str(units))
+    monkeypatch.setenv("DSG_LZ_TAIL", "0")      # no 64 KiB tail chunks beyond the remainder of the last big one
     data = synth.text_like(3_000_000, 41).numpy().tobytes() + synth.binary_like(2_000_001, 42).numpy().tobytes()
     raw = packer6.deflate(data, level=6)
     assert zlib.decompress(raw, -15) == data
