@@ -9,6 +9,9 @@
 namespace dsg {
 
 // May read up to 3 bytes beyond src+n inside the last aligned 32-bit word (never across it).
+// kStreamStore: the 128-bit stores carry the evict-first hint (data that is written once and read much later by
+// another kernel should not push the working set out of L2).
+template <bool kStreamStore = false>
 DSG_D void block_copy_unaligned(uint8_t *__restrict__ dst, const uint8_t *__restrict__ src, uint64_t n, uint32_t tid,
                                 uint32_t nthr) {
   if (n == 0) return;
@@ -32,7 +35,12 @@ DSG_D void block_copy_unaligned(uint8_t *__restrict__ dst, const uint8_t *__rest
       v = make_uint4(__funnelshift_r(a0, a1, sh), __funnelshift_r(a1, a2, sh), __funnelshift_r(a2, a3, sh),
                      __funnelshift_r(a3, a4, sh));
     }
+#if defined(DSG_EMU)
     *reinterpret_cast<uint4 *>(d + w * 16) = v;
+#else
+    if (kStreamStore) __stcs(reinterpret_cast<uint4 *>(d + w * 16), v);
+    else *reinterpret_cast<uint4 *>(d + w * 16) = v;
+#endif
   }
   for (uint64_t i = head + body * 16 + tid; i < n; i += nthr) dst[i] = src[i];
 }
