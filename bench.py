@@ -201,11 +201,30 @@ def run_reference(args, rank, world):
                                    "CPU restatement of archive/tar + gzip (zlib level 6), Go toolchain absent"},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(json.dumps(line))
     return 0
 
 
+_STDOUT_FD = None
+
+
+def quiet_stdout():
+    """stdout carries exactly ONE line, the JSON result: libraries that print to file descriptor 1 from native code
+    (NCCL's version banner at communicator creation) are sent to stderr for the life of the process."""
+    global _STDOUT_FD
+    if _STDOUT_FD is None:
+        sys.stdout.flush()
+        _STDOUT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(text):
+    sys.stdout.flush()
+    os.write(_STDOUT_FD if _STDOUT_FD is not None else 1, (text + "\n").encode())
+
+
 def main():
+    quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
@@ -232,10 +251,6 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        # NCCL prints its version banner on stdout at the VERSION level (the box's default): keep stdout to the one
-        # JSON line. An explicit INFO / TRACE setting of the caller is left alone.
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
 
     def barrier():
@@ -390,7 +405,7 @@ def main():
         "size_ratio_vs_zlib6": size_ratio,
     }
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(json.dumps(line))
     for b in (d_entries, d_strtab, d_out):
         b.free()
     h_arena.free()
