@@ -397,7 +397,7 @@ def main():
                      "traffic_source": "profiles/r01_lz_traffic.json (ncu dram__bytes_read.sum + dram__bytes_write.sum "
                                        "of one launch of this workload)", "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg_bytes,
-                     "note": "not HBM bound: dependent chain walks in shared memory, 51 % issue-slot use, 45 % of warp "
+                     "note": "not HBM bound: dependent chain walks in shared memory, 50 % issue-slot use, 48 % of warp "
                              "time at barriers (profiles/r01_lz_ncu.md)"},
         "cpu_baseline": cpu_baseline,
         "clocks": clocks,
