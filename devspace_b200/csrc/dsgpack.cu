@@ -761,9 +761,13 @@ int file_crc_run(dsg_ctx *ctx, const dsg_entry *d_entries, uint32_t n, const uin
   CU(cudaStreamSynchronize(st));
   if (h[1]) return fail(ctx, DSG_E_RANGE, "entry %u: payload range outside the arena", h[1] - 1);
   const uint32_t nunits = h[0];
-  CU(ctx->fc_raw.ensure(sizeof(uint32_t) * ((size_t)nunits + 1)));
+  CU(ctx->fc_raw.ensure(sizeof(uint32_t) * (2 * (size_t)nunits + 2)));  // remainders, then the unit -> file map
+  uint32_t *unit_file = ctx->fc_raw.as<uint32_t>() + nunits + 1;
   if (nunits) {
-    fcrc_units_kernel<<<nunits, kCrcThreads, 0, st>>>(files, n, d_arena, first, ctx->crc_tab.as<uint32_t>(),
+    fcrc_map_kernel<<<(n + 255) / 256, 256, 0, st>>>(first, n, unit_file);
+    LAUNCH_CHECK();
+    fcrc_units_kernel<<<(nunits + kFileCrcUnitsPerCta - 1) / kFileCrcUnitsPerCta, kCrcThreads, 0, st>>>(
+        files, n, d_arena, first, unit_file, nunits, ctx->crc_tab.as<uint32_t>(),
                                                        ctx->crc_shift.as<uint32_t>(), ctx->fc_raw.as<uint32_t>());
     LAUNCH_CHECK();
   }

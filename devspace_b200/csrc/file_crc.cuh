@@ -104,58 +104,63 @@ fcrc_scan_add_kernel(uint32_t *__restrict__ out, uint32_t n, const uint32_t *__r
   if (i == 0) out[n] = *grand;
 }
 
-// One CTA per unit: raw remainder of the unit's bytes. first[] = exclusive scan of the unit counts (n + 1 entries).
+// unit_file[u] = the file unit u belongs to (thread per file; a binary search per unit in the units kernel cost 17
+// dependent global loads per unit, most of the time of a tree of small files)
+__global__ void fcrc_map_kernel(const uint32_t *__restrict__ first, uint32_t n, uint32_t *__restrict__ unit_file) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  for (uint32_t u = first[i]; u < first[i + 1]; u++) unit_file[u] = i;
+}
+
+// One CTA per kFileCrcUnitsPerCta consecutive units (the 21 KB of lookup tables are loaded once per CTA: with one
+// unit per CTA a tree of 100 000 small files spent its time loading tables): raw remainder of each unit's bytes.
+// first[] = exclusive scan of the unit counts (n + 1 entries).
+constexpr int kFileCrcUnitsPerCta = 8;
+
 __global__ void __launch_bounds__(kCrcThreads)
 fcrc_units_kernel(const FileCrcEntry *__restrict__ files, uint32_t n, const uint8_t *__restrict__ arena,
-                  const uint32_t *__restrict__ first, const uint32_t *__restrict__ g_tab,
+                  const uint32_t *__restrict__ first, const uint32_t *__restrict__ unit_file, uint32_t nunits,
+                  const uint32_t *__restrict__ g_tab,
                   const uint32_t *__restrict__ g_shift, uint32_t *__restrict__ raw_out) {
   __shared__ uint32_t T[kCrcTables * 256];
   __shared__ uint32_t S[kCrcShiftEntries];
   __shared__ uint32_t red[kCrcThreads / 32];
-  __shared__ uint32_t s_file;
   for (int i = threadIdx.x; i < kCrcTables * 256; i += kCrcThreads) T[i] = g_tab[i];
   for (int i = threadIdx.x; i < kCrcShiftEntries; i += kCrcThreads) S[i] = g_shift[i];
-  const uint32_t u = blockIdx.x;
-  if (threadIdx.x == 0) {  // the file whose unit range holds u: last i with first[i] <= u
-    uint32_t lo = 0, hi = n;
-    while (hi - lo > 1) {
-      const uint32_t mid = (lo + hi) >> 1;
-      if (first[mid] <= u) lo = mid;
-      else hi = mid;
-    }
-    s_file = lo;
-  }
-  __syncthreads();
-  const uint32_t f = s_file;
-  const uint64_t size = files[f].size;
-  const uint8_t *p = arena + files[f].off;
-  const uint32_t head = fcrc_head_len((uint64_t)(uintptr_t)p, size);
-  const uint64_t body = (size - head) & ~15ull;
-  const uint64_t b0 = (uint64_t)(u - first[f]) * kFileCrcUnit;
-  const uint64_t nbytes = body - b0 < (uint64_t)kFileCrcUnit ? body - b0 : (uint64_t)kFileCrcUnit;
-  const uint4 *base = reinterpret_cast<const uint4 *>(p + head + b0);
-  const uint32_t nw = (uint32_t)(nbytes / 16);
-  uint32_t acc = 0, last = 0;
-  bool any = false;
   const uint32_t *MK = T + 16 * 256;
-  for (uint32_t w = threadIdx.x; w < nw; w += kCrcThreads) {
-    const uint4 v = base[w];
-    acc = MK[acc & 0xff] ^ MK[256 + ((acc >> 8) & 0xff)] ^ MK[512 + ((acc >> 16) & 0xff)] ^ MK[768 + (acc >> 24)];
-    acc ^= crc_raw16(T, v);
-    last = w;
-    any = true;
-  }
-  if (any) {
-    const uint32_t after = nw - 1 - last;
-    acc = crc_mul(acc, after < (uint32_t)kCrcShiftEntries ? S[after] : crc_xpow8((uint64_t)after * 16));
-  }
-  for (int o = 16; o > 0; o >>= 1) acc ^= __shfl_xor_sync(0xffffffffu, acc, o);
-  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    uint32_t r = 0;
-    for (int i = 0; i < kCrcThreads / 32; i++) r ^= red[i];
-    raw_out[u] = r;
+  const uint32_t u0 = blockIdx.x * kFileCrcUnitsPerCta;
+  for (uint32_t u = u0; u < u0 + kFileCrcUnitsPerCta && u < nunits; u++) {
+    __syncthreads();  // tables loaded; red of the previous unit consumed
+    const uint32_t f = unit_file[u];
+    const uint64_t size = files[f].size;
+    const uint8_t *p = arena + files[f].off;
+    const uint32_t head = fcrc_head_len((uint64_t)(uintptr_t)p, size);
+    const uint64_t body = (size - head) & ~15ull;
+    const uint64_t b0 = (uint64_t)(u - first[f]) * kFileCrcUnit;
+    const uint64_t nbytes = body - b0 < (uint64_t)kFileCrcUnit ? body - b0 : (uint64_t)kFileCrcUnit;
+    const uint4 *base = reinterpret_cast<const uint4 *>(p + head + b0);
+    const uint32_t nw = (uint32_t)(nbytes / 16);
+    uint32_t acc = 0, last = 0;
+    bool any = false;
+    for (uint32_t w = threadIdx.x; w < nw; w += kCrcThreads) {
+      const uint4 v = base[w];
+      acc = MK[acc & 0xff] ^ MK[256 + ((acc >> 8) & 0xff)] ^ MK[512 + ((acc >> 16) & 0xff)] ^ MK[768 + (acc >> 24)];
+      acc ^= crc_raw16(T, v);
+      last = w;
+      any = true;
+    }
+    if (any) {
+      const uint32_t after = nw - 1 - last;
+      acc = crc_mul(acc, after < (uint32_t)kCrcShiftEntries ? S[after] : crc_xpow8((uint64_t)after * 16));
+    }
+    for (int o = 16; o > 0; o >>= 1) acc ^= __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t r = 0;
+      for (int i = 0; i < kCrcThreads / 32; i++) r ^= red[i];
+      raw_out[u] = r;
+    }
   }
 }
 
@@ -179,11 +184,12 @@ fcrc_join_kernel(const FileCrcEntry *__restrict__ files, uint32_t n, const uint8
     const uint32_t per = (nu + 31) / 32;
     const uint32_t lo = lane * per, hi = lo + per < nu ? lo + per : nu;
     if (lo < hi) {
-      const uint32_t k_full = crc_xpow8(kFileCrcUnit);
+      const uint32_t k_full = hi - lo > 1 ? crc_xpow8(kFileCrcUnit) : 0u;  // (a power costs ~40 multiplications)
       const uint64_t last_len = body - (uint64_t)(nu - 1) * kFileCrcUnit;
-      for (uint32_t k = lo; k < hi; k++) {
+      acc = raw[u0 + lo];
+      for (uint32_t k = lo + 1; k < hi; k++) {
         const uint32_t mult = (k == nu - 1) ? crc_xpow8(last_len) : k_full;
-        acc = (k == lo ? 0u : crc_mul(acc, mult)) ^ raw[u0 + k];
+        acc = crc_mul(acc, mult) ^ raw[u0 + k];
       }
       uint64_t end = (uint64_t)hi * kFileCrcUnit;
       if (end > body) end = body;
@@ -191,6 +197,12 @@ fcrc_join_kernel(const FileCrcEntry *__restrict__ files, uint32_t n, const uint8
     }
   }
   for (int o = 16; o > 0; o >>= 1) acc ^= __shfl_xor_sync(0xffffffffu, acc, o);
+  // The two remaining powers are computed side by side on lanes 1 and 2: for a tree of small files these powers,
+  // on one lane of an otherwise idle warp, were most of the kernel's time.
+  uint32_t pw = 0;
+  if (lane == 1 && head) pw = crc_xpow8(body + tail);
+  if (lane == 2 && size) pw = crc_xpow8(size);
+  const uint32_t pw_head = __shfl_sync(0xffffffffu, pw, 1), pw_size = __shfl_sync(0xffffffffu, pw, 2);
   if (lane == 0) {
     auto raw_bytes = [](const uint8_t *q, uint32_t m) {
       uint32_t c = 0;
@@ -200,9 +212,9 @@ fcrc_join_kernel(const FileCrcEntry *__restrict__ files, uint32_t n, const uint8
       }
       return c;
     };
-    if (head) acc ^= crc_mul(raw_bytes(p, head), crc_xpow8(body + tail));
+    if (head) acc ^= crc_mul(raw_bytes(p, head), pw_head);
     if (tail) acc ^= raw_bytes(p + head + body, tail);
-    crcs[f] = size ? crc_finalise(acc, size) : 0u;
+    crcs[f] = size ? (acc ^ crc_mul(0xffffffffu, pw_size) ^ 0xffffffffu) : 0u;  // crc_finalise with the power given
   }
 }
 

@@ -152,10 +152,12 @@ int emu_file_crc32(const uint8_t *entries, uint32_t n, uint32_t stride, uint32_t
   emu::launch(dim3(nblk), dim3(kScanBlock), 0, [&] { fcrc_scan_add_kernel(first.data(), n, totals.data(), grand); });
   if (*error) return -(int)*error;
   const uint32_t nunits = *grand;
-  std::vector<uint32_t> raw(nunits + 1);
+  std::vector<uint32_t> raw(nunits + 1), unit_file(nunits + 1);
   if (nunits)
-    emu::launch(dim3(nunits), dim3(kCrcThreads), 0, [&] {
-      fcrc_units_kernel(files.data(), n, arena, first.data(), tab.data(), shift.data(), raw.data());
+    emu::launch(dim3((n + 255) / 256), dim3(256), 0, [&] { fcrc_map_kernel(first.data(), n, unit_file.data()); });
+  if (nunits)
+    emu::launch(dim3((nunits + kFileCrcUnitsPerCta - 1) / kFileCrcUnitsPerCta), dim3(kCrcThreads), 0, [&] {
+      fcrc_units_kernel(files.data(), n, arena, first.data(), unit_file.data(), nunits, tab.data(), shift.data(), raw.data());
     });
   emu::launch(dim3((n + 7) / 8), dim3(256), 0,
               [&] { fcrc_join_kernel(files.data(), n, arena, first.data(), raw.data(), crcs); });
