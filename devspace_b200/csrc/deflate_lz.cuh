@@ -542,8 +542,21 @@ DSG_D void search_way_setup(SearchWay &w, const uint8_t *s_data, const uint16_t 
     w.depth = w.best >= kNice ? 0 : (w.best >= kGood ? kDepth / 4 : kDepth);
     w.q = s_prev[w.slot];
     w.aw = w.a[w.best];  // the byte a longer match has to reproduce (cheap first filter)
-    if (v == w.v_prev && w.max_back > 0 && w.best < kNice && !(w.bdist == 1 && w.best >= kMinMatch)) {
-      // interior of a byte run: try the distance-1 candidate (never in the chains, see insert_one)
+    const bool in_run = v == w.v_prev && w.max_back > 0;  // interior of a byte run
+    if (w.inh_len >= kMaxMatch && w.best >= kMinMatch && w.best < w.maxlen) {
+      // The predecessor's match was cut by the length limit, so the inherited one (a byte shorter) very likely goes
+      // on: without this the lengths inside a long run or a long periodic stretch decay 258, 257, 256 ... and the
+      // parse pays extra bits for the odd lengths (a megabyte of zeros: 3.7 KB instead of 1.3 KB). Extend it from
+      // where it ends, at the same distance: one or two compare steps.
+      int cslot = (int)w.slot - w.bdist;
+      if (cslot < 0) cslot += kRing;
+      w.cb = s_data + cslot;
+      w.cd = w.bdist;
+      w.cl = w.best & ~3;
+      w.qn = w.q;
+      w.st = kCmp;
+    } else if (in_run && w.best < kNice && !(w.bdist == 1 && w.best >= kMinMatch)) {
+      // try the distance-1 candidate (never in the chains, see insert_one)
       w.cb = w.a - 1 + (w.slot == 0 ? kRing : 0);
       w.cd = 1;
       w.cl = 4;  // v == v_prev: the first four bytes are known to match
