@@ -14,10 +14,12 @@ DSG_E_ARG, DSG_E_CUDA, DSG_E_HEADER, DSG_E_TYPEFLAG = -1, -2, -3, -4
 DSG_E_CAPACITY, DSG_E_UNCLEAN_NAME, DSG_E_NOMEM, DSG_E_RANGE = -5, -6, -7, -8
 DSG_LEVEL_STORED, DSG_LEVEL_DEFAULT = 0, 6
 DSG_F_NO_TRAILER = 1
+DSG_LZ_TAIL_SET, DSG_LZ_PROFILE = 1, 2
 
 # every symbol include/dsgpack.h declares (tests check that the library exports all of them)
 SYMBOLS = [
     "dsg_abi_version", "dsg_strerror", "dsg_device_count", "dsg_last_error", "dsg_ctx_create", "dsg_ctx_destroy",
+    "dsg_ctx_set_opts",
     "dsg_pinned_alloc", "dsg_pinned_free", "dsg_entry_header_bytes", "dsg_tar_size", "dsg_gzip_bound",
     "dsg_shard_bounds", "dsg_stitch_members", "dsg_pack", "dsg_pack_tar_only", "dsg_pack_fd", "dsg_pack_device", "dsg_get_stats", "dsg_dev_tar_build",
     "dsg_dev_crc32", "dsg_dev_deflate", "dsg_dev_gzip", "dsg_dev_alloc", "dsg_dev_free", "dsg_dev_upload",
@@ -28,7 +30,8 @@ SYMBOLS = [
 
 class DsgOpts(ctypes.Structure):
     _fields_ = [("struct_size", c_uint32), ("level", c_int32), ("segment_bytes", c_uint64), ("flags", c_uint32),
-                ("reserved", c_uint32)]
+                ("reserved", c_uint32), ("lz_chunk_units", c_uint32), ("lz_run_chunks", c_uint32),
+                ("lz_grid", c_uint32), ("lz_flags", c_uint32), ("lz_tail_bytes", c_uint64)]
 
 
 class DsgStats(ctypes.Structure):
@@ -77,6 +80,7 @@ def load(build_if_missing: bool = True):
     lib.dsg_ctx_create.argtypes = [c_int, POINTER(DsgOpts), POINTER(vp)]
     lib.dsg_ctx_destroy.argtypes = [vp]
     lib.dsg_ctx_destroy.restype = None
+    lib.dsg_ctx_set_opts.argtypes = [vp, POINTER(DsgOpts)]
     lib.dsg_pinned_alloc.argtypes = [vp, sz]
     lib.dsg_pinned_alloc.restype = vp
     lib.dsg_pinned_free.argtypes = [vp, vp]

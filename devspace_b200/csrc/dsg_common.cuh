@@ -35,9 +35,11 @@ constexpr int kBlock = 512;  // tar block size (archive/tar format.go: blockSize
 DSG_HD uint64_t pad512(uint64_t n) { return (n + 511u) & ~uint64_t(511); }
 
 // Device-side status word: first error wins (lowest entry index), see dsg_status.
-struct DevStatus {
+// One 64-bit word (little endian: code in the low half, entry in the high half) updated with a single atomicMin.
+struct alignas(8) DevStatus {
   int code;            // dsg_status, 0 = ok
   unsigned int entry;  // index of the offending entry
 };
+static_assert(sizeof(DevStatus) == 8, "DevStatus is one 64-bit word");
 
 }  // namespace dsg

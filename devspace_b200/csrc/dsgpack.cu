@@ -252,11 +252,15 @@ int crc_reset(dsg_ctx *ctx) {
 
 // ---- stage: deflate -----------------------------------------------------------------------------------------
 
-__global__ void gzip_frame_kernel(uint8_t *out, const uint64_t *deflate_bytes, const uint32_t *crc_state) {
+// out_cap >= 18 (checked by the caller). *deflate_bytes is the NEEDED size when the deflate stage found the output
+// too small (*error != 0, nothing was written): the trailer then lies beyond the buffer and must not be written.
+__global__ void gzip_frame_kernel(uint8_t *out, uint64_t out_cap, const uint64_t *deflate_bytes,
+                                  const uint32_t *crc_state, const uint32_t *error) {
   // compress/gzip Writer: 1f 8b 08 00 | mtime 0 | XFL 0 | OS ff ... CRC32 LE, ISIZE LE
   if (threadIdx.x == 0) {
     const uint8_t hdr[10] = {0x1f, 0x8b, 0x08, 0, 0, 0, 0, 0, 0, 0xff};
     for (int i = 0; i < 10; i++) out[i] = hdr[i];
+    if (*error != 0 || *deflate_bytes > out_cap - 18) return;
     uint8_t *t = out + 10 + *deflate_bytes;
     const uint32_t crc = crc_state[0], isize = crc_state[1];
     for (int i = 0; i < 4; i++) t[i] = (uint8_t)(crc >> (8 * i));
@@ -315,6 +319,43 @@ __global__ void lz_finish_empty_kernel(uint8_t *out, uint64_t *total_out, int wr
   }
 }
 
+// Launch geometry of one level-6 launch over `len` bytes: the one place that decides it (the launch itself and the
+// code that pre-sizes the scratch buffers of the pipelined path both ask here).
+struct LzGeometry {
+  uint32_t chunk_bytes, run_chunks, nchunks, big_runs, big_chunks, grid;
+  size_t slot_bytes;  // scratch for the per-chunk output slots
+};
+bool lz_geometry(const dsg_ctx *ctx, uint64_t len, LzGeometry &G) {
+  const dsg_opts &o = ctx->opts;
+  // Chunk size: the largest of 64 / 128 / 256 KiB that still leaves every SM eight chunks (see kMaxChunk).
+  uint32_t chunk_bytes = kChunk;
+  while (chunk_bytes < (uint32_t)kMaxChunk && len / (2ull * chunk_bytes) >= 8ull * (uint64_t)ctx->sm_count) chunk_bytes *= 2;
+  if (o.lz_chunk_units == 1 || o.lz_chunk_units == 2 || o.lz_chunk_units == 4) chunk_bytes = o.lz_chunk_units * kChunk;
+  // Runs of run_chunks big chunks first (long runs amortise hashing the dictionary); the last half run per SM is cut
+  // into 64 KiB chunks and handed out one by one, so that the CTAs finish within a millisecond of each other.
+  const uint64_t big_total = (len + chunk_bytes - 1) / chunk_bytes;
+  uint32_t run_chunks = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(8, big_total / (4 * (uint64_t)ctx->sm_count)));
+  if (o.lz_run_chunks > 0 && o.lz_run_chunks <= 64) run_chunks = o.lz_run_chunks;
+  uint64_t tail_bytes = run_chunks > 1 || chunk_bytes > (uint32_t)kChunk
+                            ? std::min<uint64_t>(len, (uint64_t)ctx->sm_count * run_chunks * chunk_bytes / 2)
+                            : len;
+  if (o.lz_flags & DSG_LZ_TAIL_SET) tail_bytes = std::min<uint64_t>(len, o.lz_tail_bytes);
+  const uint64_t big_runs64 = (len - tail_bytes) / ((uint64_t)run_chunks * chunk_bytes);
+  const uint64_t big_chunks64 = big_runs64 * run_chunks;
+  const uint64_t nchunks64 = big_chunks64 + (len - big_chunks64 * chunk_bytes + kChunk - 1) / kChunk;
+  if (nchunks64 > 0xfffffff0ull) return false;
+  G.chunk_bytes = chunk_bytes;
+  G.run_chunks = run_chunks;
+  G.nchunks = (uint32_t)nchunks64;
+  G.big_runs = (uint32_t)big_runs64;
+  G.big_chunks = (uint32_t)big_chunks64;
+  const uint32_t nruns = G.big_runs + (G.nchunks - G.big_chunks);
+  G.grid = std::min<uint32_t>(std::max<uint32_t>(nruns, 1), (uint32_t)ctx->sm_count);
+  if (o.lz_grid > 0 && o.lz_grid < G.grid) G.grid = o.lz_grid;
+  G.slot_bytes = (size_t)lz_slot_bytes(chunk_bytes) * G.nchunks;  // every chunk, also a 64 KiB one, has a big slot
+  return true;
+}
+
 // Level-6 deflate of d_in[0,len) on `stream`: one persistent kernel. d_dict/dict_len: up to 32 KiB of the
 // member that precede d_in (previous pipeline segment). The produced size is written to *d_total (device),
 // a too-small d_out sets *d_error (device) to 1.
@@ -330,40 +371,14 @@ int lz_launch(dsg_ctx *ctx, cudaStream_t stream, const uint8_t *d_in, uint64_t l
     LAUNCH_CHECK();
     return DSG_OK;
   }
-  // Chunk size: the largest of 64 / 128 / 256 KiB that still leaves every SM eight chunks (see kMaxChunk).
-  uint32_t chunk_bytes = kChunk;
-  while (chunk_bytes < (uint32_t)kMaxChunk && len / (2ull * chunk_bytes) >= 8ull * (uint64_t)ctx->sm_count) chunk_bytes *= 2;
-  if (const char *g = getenv("DSG_LZ_CHUNK")) {  // development aid: 1, 2 or 4 units of 64 KiB
-    const long v = strtol(g, nullptr, 10);
-    if (v == 1 || v == 2 || v == 4) chunk_bytes = (uint32_t)v * kChunk;
-  }
-  // Runs of run_chunks big chunks first (long runs amortise hashing the dictionary); the last half run per SM is cut
-  // into 64 KiB chunks and handed out one by one, so that the CTAs finish within a millisecond of each other.
-  const uint64_t big_total = (len + chunk_bytes - 1) / chunk_bytes;
-  uint32_t run_chunks = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(8, big_total / (4 * (uint64_t)ctx->sm_count)));
-  if (const char *g = getenv("DSG_LZ_RUN")) {
-    const long v = strtol(g, nullptr, 10);
-    if (v > 0 && v <= 64) run_chunks = (uint32_t)v;
-  }
-  uint64_t tail_bytes = run_chunks > 1 || chunk_bytes > (uint32_t)kChunk
-                            ? std::min<uint64_t>(len, (uint64_t)ctx->sm_count * run_chunks * chunk_bytes / 2)
-                            : len;
-  if (const char *g = getenv("DSG_LZ_TAIL")) tail_bytes = std::min<uint64_t>(len, strtoull(g, nullptr, 10));  // tests
-  const uint64_t big_runs64 = (len - tail_bytes) / ((uint64_t)run_chunks * chunk_bytes);
-  const uint64_t big_chunks64 = big_runs64 * run_chunks;
-  const uint64_t nchunks64 = big_chunks64 + (len - big_chunks64 * chunk_bytes + kChunk - 1) / kChunk;
-  if (nchunks64 > 0xfffffff0ull) return fail(ctx, DSG_E_ARG, "input too large for one call");
-  const uint32_t nchunks = (uint32_t)nchunks64, big_runs = (uint32_t)big_runs64, big_chunks = (uint32_t)big_chunks64;
-  const uint32_t nruns = big_runs + (nchunks - big_chunks);
-  uint32_t grid = std::min<uint32_t>(nruns, (uint32_t)ctx->sm_count);
-  if (const char *g = getenv("DSG_LZ_GRID")) {  // debugging aid: fewer CTAs => more chunks per CTA
-    const long v = strtol(g, nullptr, 10);
-    if (v > 0 && (uint32_t)v < grid) grid = (uint32_t)v;
-  }
+  LzGeometry G;
+  if (!lz_geometry(ctx, len, G)) return fail(ctx, DSG_E_ARG, "input too large for one call");
+  const uint32_t chunk_bytes = G.chunk_bytes, run_chunks = G.run_chunks, nchunks = G.nchunks, big_runs = G.big_runs,
+                 big_chunks = G.big_chunks, grid = G.grid;
   // scratch: per-chunk output slots + sizes + offsets, the ticket word, token slots (one per resident CTA)
   const size_t meta_bytes = (sizeof(uint64_t) + sizeof(uint32_t)) * (size_t)nchunks + 64;
   CU(b_sizes.ensure(meta_bytes));
-  CU(b_slots.ensure((size_t)lz_slot_bytes(chunk_bytes) * nchunks));
+  CU(b_slots.ensure(G.slot_bytes));
   CU(b_tok.ensure(sizeof(uint32_t) * (size_t)kTokSlotWords * ctx->sm_count));
   uint64_t *offs = b_sizes.as<uint64_t>();
   uint32_t *meta = reinterpret_cast<uint32_t *>(offs + nchunks);
@@ -383,7 +398,7 @@ int lz_launch(dsg_ctx *ctx, cudaStream_t stream, const uint8_t *d_in, uint64_t l
   P.ticket = ticket;
   P.tok_scratch = b_tok.as<uint32_t>();
   P.prof = nullptr;
-  static const bool prof_on = getenv("DSG_LZ_PROF") != nullptr;  // development aid: per-phase cycle counts on stderr
+  const bool prof_on = (ctx->opts.lz_flags & DSG_LZ_PROFILE) != 0;  // development aid: per-phase cycle counts on stderr
   if (prof_on) {
     CU(ctx->lz_prof.ensure(sizeof(unsigned long long) * kProfSlots));
     CU(cudaMemsetAsync(ctx->lz_prof.p, 0, sizeof(unsigned long long) * kProfSlots, stream));
@@ -512,6 +527,17 @@ int dsg_ctx_create(int device, const dsg_opts *opts, dsg_ctx **out) {
     return rc;
   }
   *out = ctx;
+  return DSG_OK;
+}
+
+int dsg_ctx_set_opts(dsg_ctx *ctx, const dsg_opts *opts) {
+  if (!ctx || !opts) return DSG_E_ARG;
+  std::lock_guard<std::mutex> g(ctx->mu);
+  dsg_opts o{};
+  memcpy(&o, opts, std::min<size_t>(opts->struct_size, sizeof(dsg_opts)));
+  if (o.level != DSG_LEVEL_STORED && o.level != DSG_LEVEL_DEFAULT) return fail(ctx, DSG_E_ARG, "level must be 0 or 6");
+  o.struct_size = sizeof(dsg_opts);
+  ctx->opts = o;
   return DSG_OK;
 }
 
@@ -862,7 +888,9 @@ static int gzip_device(dsg_ctx *ctx, const uint8_t *d_in, uint64_t len, int leve
     return fail(ctx, DSG_E_CAPACITY, "gzip output needs at least 18 bytes");
   }
   int rc;
+  uint64_t *sc = ctx->scalars.as<uint64_t>();
   if ((rc = crc_reset(ctx))) return rc;
+  CU(cudaMemsetAsync(sc + kSSpare, 0, sizeof(uint64_t), ctx->stream));  // the deflate stage's "too small" flag
   tic(ctx, kTimCrc);
   if ((rc = crc_update(ctx, d_in, len))) return rc;
   toc(ctx, kTimCrc);
@@ -872,8 +900,9 @@ static int gzip_device(dsg_ctx *ctx, const uint8_t *d_in, uint64_t len, int leve
     *out_len = dn + 18;
     return rc;
   }
-  uint64_t *sc = ctx->scalars.as<uint64_t>();
-  gzip_frame_kernel<<<1, 32, 0, ctx->stream>>>(d_out, sc + kSDeflateBytes, reinterpret_cast<uint32_t *>(sc + kSCrc));
+  gzip_frame_kernel<<<1, 32, 0, ctx->stream>>>(d_out, out_cap, sc + kSDeflateBytes,
+                                               reinterpret_cast<uint32_t *>(sc + kSCrc),
+                                               reinterpret_cast<uint32_t *>(sc + kSSpare));
   LAUNCH_CHECK();
   CU(cudaMemcpyAsync(ctx->h_scalars, sc, sizeof(uint64_t) * kScalarWords, cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
@@ -1073,9 +1102,12 @@ static int pack_host_pipelined(dsg_ctx *ctx, const dsg_entry *entries, size_t n,
     }
   }
   if (gzip && ctx->opts.level != DSG_LEVEL_STORED) {
-    const uint64_t nch = (std::min(S, T) + kChunk - 1) / kChunk;
-    CU(ctx->chunk_sizes.ensure((sizeof(uint64_t) + sizeof(uint32_t)) * (size_t)nch + 64));
-    CU(ctx->chunk_slots.ensure((size_t)lz_slot_bytes(kChunk) * nch));  // covers every chunk size: fewer, larger slots
+    // Sized with the launch's own arithmetic for the largest segment, so that no launch of the pipeline has to
+    // re-allocate (cudaFree + cudaMalloc synchronise the device in the middle of the overlap).
+    LzGeometry G;
+    if (!lz_geometry(ctx, std::min(S, T), G)) return fail(ctx, DSG_E_ARG, "segment too large for one launch");
+    CU(ctx->chunk_sizes.ensure((sizeof(uint64_t) + sizeof(uint32_t)) * (size_t)G.nchunks + 64));
+    CU(ctx->chunk_slots.ensure(G.slot_bytes));
     CU(ctx->lz_scratch.ensure(sizeof(uint32_t) * (size_t)kTokSlotWords * ctx->sm_count));
   }
   if (gzip) {

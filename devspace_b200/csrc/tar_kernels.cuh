@@ -26,9 +26,10 @@ constexpr int kLayoutThreads = 256;
 constexpr int kRowWords = 129;             // 512 B + 4 B skew: row r, word w -> bank (r + w) % 32
 
 DSG_D void report_error(DevStatus *st, int code, unsigned int entry) {
-  // first error = lowest entry index
-  unsigned int prev = atomicMin(&st->entry, entry);
-  if (entry <= prev) st->code = code;
+  // first error = lowest entry index. Entry (high half) and code (low half) travel in ONE 64-bit atomicMin, so the
+  // code that the host reads always belongs to the entry it reads.
+  const unsigned long long w = ((unsigned long long)entry << 32) | (unsigned long long)(unsigned int)code;
+  atomicMin(reinterpret_cast<unsigned long long *>(st), w);
 }
 
 // ---- plan -------------------------------------------------------------------------------------------

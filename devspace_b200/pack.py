@@ -91,9 +91,11 @@ class DeviceManifest:
 class Packer:
     """One dsg_ctx: one GPU, one caller at a time (SURVEY.md 8b "Threading")."""
 
-    def __init__(self, device: int = 0, level: int = _lib.DSG_LEVEL_DEFAULT, segment_bytes: int = 0, flags: int = 0):
+    def __init__(self, device: int = 0, level: int = _lib.DSG_LEVEL_DEFAULT, segment_bytes: int = 0, flags: int = 0,
+                 **lz):
         self._lib = _lib.load()
-        opts = DsgOpts(ctypes.sizeof(DsgOpts), level, segment_bytes, flags, 0)
+        self._base = (level, segment_bytes, flags)
+        opts = self._opts(**lz)
         ctx = c_void_p()
         rc = self._lib.dsg_ctx_create(device, byref(opts), byref(ctx))
         if rc != 0:
@@ -104,6 +106,19 @@ class Packer:
         self.level = level
 
     # -- plumbing -------------------------------------------------------------------------------------
+    def _opts(self, chunk_units: int = 0, run_chunks: int = 0, grid: int = 0, tail_bytes: Optional[int] = None,
+              profile: bool = False) -> DsgOpts:
+        level, segment_bytes, flags = self._base
+        lz_flags = (_lib.DSG_LZ_TAIL_SET if tail_bytes is not None else 0) | (_lib.DSG_LZ_PROFILE if profile else 0)
+        return DsgOpts(ctypes.sizeof(DsgOpts), level, segment_bytes, flags, 0, chunk_units, run_chunks, grid, lz_flags,
+                       int(tail_bytes or 0))
+
+    def set_lz_geometry(self, **lz) -> None:
+        """dsg_ctx_set_opts: launch geometry of the level-6 kernel (chunk_units, run_chunks, grid, tail_bytes,
+        profile); no arguments = automatic. Used by the parity tests and the profiling tools."""
+        opts = self._opts(**lz)
+        self._check(self._lib.dsg_ctx_set_opts(self._ctx, byref(opts)))
+
     def close(self):
         if getattr(self, "_ctx", None):
             self._lib.dsg_ctx_destroy(self._ctx)

@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define DSG_ABI_VERSION 1
+#define DSG_ABI_VERSION 2
 
 typedef enum dsg_status {
   DSG_OK = 0,
@@ -82,9 +82,18 @@ typedef struct dsg_opts {
                             * between 64 and 512 MiB)                                            */
   uint32_t flags;          /* DSG_F_*                                                                */
   uint32_t reserved;
+  /* Launch geometry of the level-6 kernel. All zero (the default) = chosen from the input size. The parity
+   * tests and the profiling tools set these to reach every geometry with small inputs; a caller never has to. */
+  uint32_t lz_chunk_units; /* deflate chunk = 1, 2 or 4 units of 64 KiB (0 = automatic)                    */
+  uint32_t lz_run_chunks;  /* consecutive chunks one CTA compresses with one sliding window, 1..64 (0 = auto) */
+  uint32_t lz_grid;        /* CTAs of the launch (0 = one per SM)                                           */
+  uint32_t lz_flags;       /* DSG_LZ_*                                                                      */
+  uint64_t lz_tail_bytes;  /* with DSG_LZ_TAIL_SET: bytes at the end of a launch handed out in 64 KiB chunks */
 } dsg_opts;
 
 #define DSG_F_NO_TRAILER 1u /* omit the 1024-byte tar trailer: for every shard but the last */
+#define DSG_LZ_TAIL_SET 1u  /* lz_tail_bytes is meaningful (0 is a valid value)                             */
+#define DSG_LZ_PROFILE 2u   /* per-phase cycle counts of the level-6 kernel on stderr (development aid)     */
 
 /* Per-call timing and size counters (bench.py reads them; times are CUDA-event milliseconds). */
 typedef struct dsg_stats {
@@ -112,6 +121,8 @@ typedef struct dsg_stats {
  * here the context owns the device, streams and reusable device/pinned buffers. */
 int dsg_ctx_create(int device, const dsg_opts *opts, dsg_ctx **out);
 void dsg_ctx_destroy(dsg_ctx *ctx);
+/* Replaces the options of a live context (level, segment size, flags, launch geometry) between calls. */
+int dsg_ctx_set_opts(dsg_ctx *ctx, const dsg_opts *opts);
 const char *dsg_last_error(const dsg_ctx *ctx);   /* text of the last failure (CUDA error string etc.) */
 const char *dsg_strerror(int status);
 int dsg_abi_version(void);

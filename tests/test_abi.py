@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol():
     for s in declared:
         assert hasattr(lib, s), f"{s} declared in include/dsgpack.h but not exported"
     assert sorted(_lib.SYMBOLS) == declared
-    assert lib.dsg_abi_version() == 1
+    assert lib.dsg_abi_version() == 2
 
 
 def test_entry_struct_layout_is_80_bytes():

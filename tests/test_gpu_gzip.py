@@ -1,6 +1,7 @@
 """GPU: CRC32, deflate and the whole dsg_pack path through the C ABI.
 Judged equalities: gunzip(out) == oracle tar stream byte for byte; stock decoders accept the
 output; compressed size within 3 % of the oracle's zlib level-6 size (level 6 only)."""
+import ctypes
 import gzip
 import os
 import shutil
@@ -270,16 +271,61 @@ def test_level6_output_is_deterministic_and_equals_the_emulator(packer6):
 
 
 @pytest.mark.parametrize("units", [2, 4])
-def test_level6_large_chunks(packer6, units, monkeypatch):
+def test_level6_large_chunks(packer6, units):
     """Inputs of hundreds of MB are cut into 128 / 256 KiB chunks (one deflate block each) with 64 KiB chunks at the
-    end of the launch; DSG_LZ_CHUNK / DSG_LZ_TAIL force that on a small input: the stream must inflate, stay within the size bound, and equal the emulator's bytes."""
+    end of the launch; dsg_opts.lz_chunk_units / lz_tail_bytes force that on a small input: the stream must inflate,
+    stay within the size bound, and equal the emulator's bytes."""
     from devspace_b200 import synth
     from test_emu_deflate import emu_deflate
-    monkeypatch.setenv("DSG_LZ_CHUNK", str(units))
-    monkeypatch.setenv("DSG_LZ_TAIL", "0")      # no 64 KiB tail chunks beyond the remainder of the last big one
-    data = synth.text_like(3_000_000, 41).numpy().tobytes() + synth.binary_like(2_000_001, 42).numpy().tobytes()
-    raw = packer6.deflate(data, level=6)
-    assert zlib.decompress(raw, -15) == data
-    assert len(raw) <= 1.03 * _zlib6(data)
-    small = data[2_900_000:3_300_000]                      # text, then binary: 400 000 bytes, a short last chunk
-    assert packer6.deflate(small, level=6) == emu_deflate(small, grid=2, run_chunks=1, chunk_units=units)
+    packer6.set_lz_geometry(chunk_units=units, tail_bytes=0)   # no 64 KiB tail chunks beyond the last big one's rest
+    try:
+        data = synth.text_like(3_000_000, 41).numpy().tobytes() + synth.binary_like(2_000_001, 42).numpy().tobytes()
+        raw = packer6.deflate(data, level=6)
+        assert zlib.decompress(raw, -15) == data
+        assert len(raw) <= 1.03 * _zlib6(data)
+        small = data[2_900_000:3_300_000]                  # text, then binary: 400 000 bytes, a short last chunk
+        assert packer6.deflate(small, level=6) == emu_deflate(small, grid=2, run_chunks=1, chunk_units=units)
+    finally:
+        packer6.set_lz_geometry()
+
+
+@pytest.mark.parametrize("level", [0, 6])
+def test_gzip_capacity_probe_never_writes_past_the_buffer(level):
+    """DSG_E_CAPACITY is the documented size probe: with a too-small device buffer dsg_dev_gzip / dsg_pack_device report
+    the size they need and leave every byte behind the buffer alone (the gzip trailer used to be written at
+    out + 10 + needed, far past a small buffer)."""
+    from devspace_b200 import synth
+    from devspace_b200._lib import DsgError
+    from devspace_b200.pack import DeviceBuffer, DeviceManifest, Packer
+    data = np.frombuffer(synth.text_like(400_000, 51).numpy().tobytes() + helpers.rng_bytes(52, 100_000), np.uint8)
+    man = from_entries(SUITE["mixed_tree"])
+    with Packer(level=level) as p:
+        d_in = DeviceBuffer(p, data.size + 16).upload(data)
+        dm = DeviceManifest(p, man)
+        ARENA = 4 << 20                                         # the output buffer is carved out of this allocation
+        d_area = DeviceBuffer(p, ARENA)
+        canary = np.full(ARENA, 0xA5, np.uint8)
+        try:
+            whole = p.deflate(data, level=level, gzip=True)
+            need = len(whole)
+            whole_pack = p.pack(man)
+            for fn, n_need, ref in ((lambda cap: p._lib.dsg_dev_gzip(p._ctx, d_in.ptr, data.size, level, d_area.ptr, cap,
+                                                                   ctypes.byref(n_out)), need, whole),
+                                    (lambda cap: p._lib.dsg_pack_device(p._ctx, dm.entries.ptr, dm.n, dm.strtab.ptr,
+                                                                      dm.strtab_len, dm.arena.ptr, dm.arena_len,
+                                                                      d_area.ptr, cap, ctypes.byref(n_out)),
+                                     len(whole_pack), whole_pack)):
+                for cap in (18, 1000, n_need - 1, n_need):
+                    d_area.upload(canary)
+                    n_out = ctypes.c_size_t()
+                    rc = fn(cap)
+                    got = d_area.download()
+                    assert (got[cap:] == 0xA5).all(), (level, cap, "bytes behind the buffer were written")
+                    if cap < n_need:
+                        assert rc == -5 and n_out.value == n_need, (level, cap, rc, n_out.value, n_need)
+                    else:
+                        assert rc == 0 and n_out.value == n_need and got[:n_need].tobytes() == ref
+        finally:
+            for b in (d_in, d_area):
+                b.free()
+            dm.free()

@@ -43,7 +43,8 @@ def check(p, name, data):
 
 def main():
     sizes = [int(x) for x in (sys.argv[1:] or ["1000000", "20000000"])]
-    with Packer(level=6) as p:
+    # LZ_PROF=1: per-phase cycle counts of the kernel on stderr (dsg_opts.lz_flags & DSG_LZ_PROFILE)
+    with Packer(level=6, profile=bool(os.environ.get("LZ_PROF")), chunk_units=int(os.environ.get("LZ_UNITS", "0"))) as p:
         for n in sizes:
             check(p, f"text[{n}]", synth.text_like(n, 1).numpy().tobytes())
             check(p, f"rand[{n}]", synth.random_bytes(n, 2).numpy().tobytes())

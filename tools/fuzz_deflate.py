@@ -42,16 +42,15 @@ def main():
                 n = max(0, n + int(rng.integers(-3, 4)))
                 parts.append(piece(rng, n, 1000 * c + k))
             data = b"".join(parts)
-            for var in ("DSG_LZ_CHUNK", "DSG_LZ_TAIL", "DSG_LZ_RUN", "DSG_LZ_GRID"):
-                os.environ.pop(var, None)
+            geo = {}
             if rng.random() < 0.5:
-                os.environ["DSG_LZ_CHUNK"] = str(int(rng.choice([1, 2, 4])))
-                os.environ["DSG_LZ_TAIL"] = str(int(rng.choice([0, 65536, 300_000, 10 ** 9])))
-                os.environ["DSG_LZ_RUN"] = str(int(rng.choice([1, 2, 3, 8])))
+                geo = dict(chunk_units=int(rng.choice([1, 2, 4])), tail_bytes=int(rng.choice([0, 65536, 300_000, 10 ** 9])),
+                           run_chunks=int(rng.choice([1, 2, 3, 8])))
             if rng.random() < 0.3:
-                os.environ["DSG_LZ_GRID"] = str(int(rng.choice([1, 2, 7, 100])))
+                geo["grid"] = int(rng.choice([1, 2, 7, 100]))
+            p.set_lz_geometry(**geo)
             raw = p.deflate(data, level=6)
-            assert zlib.decompress(raw, -15) == data, ("round trip", c, len(data), dict(os.environ))
+            assert zlib.decompress(raw, -15) == data, ("round trip", c, len(data), geo)
             co = zlib.compressobj(6, zlib.DEFLATED, -15)
             ref = len(co.compress(data) + co.flush())
             if len(data) > 100_000:
