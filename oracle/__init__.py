@@ -71,6 +71,10 @@ def _load():
                                     ctypes.POINTER(ctypes.c_size_t)]
         lib.gogzip_crc32.argtypes = [ctypes.c_void_p, ctypes.c_size_t]
         lib.gogzip_crc32.restype = ctypes.c_uint32
+        lib.gooracle_pack_shards_mt.argtypes = [ctypes.POINTER(_CEntry), ctypes.POINTER(ctypes.c_size_t),
+                                                ctypes.POINTER(ctypes.c_size_t), ctypes.c_size_t, ctypes.c_int,
+                                                ctypes.c_int, ctypes.POINTER(ctypes.c_size_t),
+                                                ctypes.POINTER(ctypes.c_size_t), ctypes.POINTER(ctypes.c_double)]
         _lib = lib
     return _lib
 
@@ -181,6 +185,42 @@ def tar_stream(entries: Sequence[Entry]) -> bytes:
         raise OracleError(rc)
     assert written.value == total.value
     return buf.raw
+
+
+def tar_stream_update(entries: Sequence[Entry], update: Callable[[memoryview], None], trailer: bool) -> int:
+    """Feeds the stream of `entries` to `update` (e.g. a hashlib object's update) without materialising a bytes copy;
+    the 1024-byte trailer of Writer.Close() only when `trailer`. For streams too large to hold twice: the caller
+    walks the header list in groups. Returns the bytes fed."""
+    lib = _load()
+    arr, _keep = _to_c(entries)
+    total = ctypes.c_size_t()
+    rc = lib.gotar_stream_size(arr, len(entries), ctypes.byref(total))
+    if rc:
+        raise OracleError(rc)
+    buf = ctypes.create_string_buffer(total.value)
+    written = ctypes.c_size_t()
+    rc = lib.gotar_write(arr, len(entries), buf, total.value, ctypes.byref(written))
+    if rc:
+        raise OracleError(rc)
+    n = total.value if trailer else total.value - 1024
+    update(memoryview(buf)[:n])
+    return n
+
+
+def pack_shards_mt(entries: Sequence[Entry], bounds: Sequence[int], threads: int, level: int = 6):
+    """One archive per shard [bounds[s], bounds[s+1]) of `entries`, packed by a pool of `threads` pthreads inside the
+    oracle (no interpreter lock in the loop). Returns (tar_bytes[], gz_bytes[], worker_seconds[]) per shard."""
+    lib = _load()
+    arr, _keep = _to_c(entries)
+    ns = len(bounds) - 1
+    SZ = ctypes.c_size_t * max(ns, 1)
+    lo, hi = SZ(*bounds[:-1]), SZ(*bounds[1:])
+    tb, gb = SZ(), SZ()
+    sec = (ctypes.c_double * max(ns, 1))()
+    rc = lib.gooracle_pack_shards_mt(arr, lo, hi, ns, level, threads, tb, gb, sec)
+    if rc:
+        raise OracleError(rc)
+    return list(tb)[:ns], list(gb)[:ns], list(sec)[:ns]
 
 
 def path_clean(p: bytes) -> bytes:

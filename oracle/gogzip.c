@@ -15,7 +15,11 @@
  * Pinning: header/trailer bytes and CRC are checked against CPython's zlib/gzip in
  * tests/test_oracle_gzip.py; decodability against GNU gzip 1.12.
  */
+#define _POSIX_C_SOURCE 200809L
+#include <pthread.h>
+#include <stdlib.h>
 #include <string.h>
+#include <time.h>
 #include <zlib.h>
 
 #include "gotar.h"
@@ -67,4 +71,69 @@ int gogzip_pack(const uint8_t *in, size_t n, int level, uint8_t *out, size_t cap
   for (int i = 0; i < 4; i++) out[op++] = (uint8_t)(isize >> (8 * i));
   *written = op;
   return 0;
+}
+
+/* ---- bench.py --impl reference: the same path on every host core ------------------------------------------------
+ * writeTar is one goroutine per archive (tar.go:146); the multi-core courtesy number of SURVEY.md 8d runs one
+ * archive per shard of the header list. A pthread pool inside the oracle keeps the interpreter's lock out of the
+ * timed loop: worker k packs shards k, k+T, ... (tar stream, then gzip at `level`), each into its own buffers.
+ * tar_bytes / gz_bytes / seconds have one slot per shard; seconds[] is the worker's own clock for that shard. */
+typedef struct {
+  const gotar_entry *es;
+  const size_t *lo, *hi;
+  size_t nshards;
+  int level, nthreads, k;
+  size_t *tar_bytes, *gz_bytes;
+  double *seconds;
+  int rc;
+} pool_job;
+
+static void *pool_worker(void *arg) {
+  pool_job *j = (pool_job *)arg;
+  for (size_t s = (size_t)j->k; s < j->nshards; s += (size_t)j->nthreads) {
+    struct timespec t0, t1;
+    clock_gettime(CLOCK_MONOTONIC, &t0);
+    const gotar_entry *es = j->es + j->lo[s];
+    const size_t n = j->hi[s] - j->lo[s];
+    size_t T = 0, W = 0, G = 0;
+    int rc = gotar_stream_size(es, n, &T);
+    if (rc) { j->rc = rc; return NULL; }
+    uint8_t *tar = (uint8_t *)malloc(T ? T : 1);
+    const size_t cap = gogzip_bound(T);
+    uint8_t *gz = (uint8_t *)malloc(cap);
+    if (!tar || !gz) { free(tar); free(gz); j->rc = GOTAR_E_NOMEM; return NULL; }
+    rc = gotar_write(es, n, tar, T, &W);
+    if (!rc) rc = gogzip_pack(tar, W, j->level, gz, cap, &G);
+    free(tar);
+    free(gz);
+    if (rc) { j->rc = rc; return NULL; }
+    clock_gettime(CLOCK_MONOTONIC, &t1);
+    j->tar_bytes[s] = W;
+    j->gz_bytes[s] = G;
+    j->seconds[s] = (double)(t1.tv_sec - t0.tv_sec) + 1e-9 * (double)(t1.tv_nsec - t0.tv_nsec);
+  }
+  return NULL;
+}
+
+int gooracle_pack_shards_mt(const gotar_entry *es, const size_t *lo, const size_t *hi, size_t nshards, int level,
+                            int nthreads, size_t *tar_bytes, size_t *gz_bytes, double *seconds) {
+  if (nthreads < 1) nthreads = 1;
+  if ((size_t)nthreads > nshards) nthreads = (int)(nshards ? nshards : 1);
+  pthread_t *th = (pthread_t *)calloc((size_t)nthreads, sizeof *th);
+  pool_job *jobs = (pool_job *)calloc((size_t)nthreads, sizeof *jobs);
+  if (!th || !jobs) { free(th); free(jobs); return GOTAR_E_NOMEM; }
+  int started = 0, rc = 0;
+  for (int k = 0; k < nthreads; k++) {
+    pool_job j = {es, lo, hi, nshards, level, nthreads, k, tar_bytes, gz_bytes, seconds, 0};
+    jobs[k] = j;
+    if (pthread_create(&th[k], NULL, pool_worker, &jobs[k]) != 0) { rc = GOTAR_E_NOMEM; break; }
+    started++;
+  }
+  for (int k = 0; k < started; k++) {
+    pthread_join(th[k], NULL);
+    if (jobs[k].rc && !rc) rc = jobs[k].rc;
+  }
+  free(th);
+  free(jobs);
+  return rc;
 }

@@ -70,6 +70,12 @@ size_t gogzip_bound(size_t n);
 int gogzip_pack(const uint8_t *in, size_t n, int level, uint8_t *out, size_t cap, size_t *written);
 uint32_t gogzip_crc32(const uint8_t *in, size_t n);
 
+
+/* One archive (tar stream + gzip at `level`) per shard [lo[s], hi[s]) of the header list, on a pool of `nthreads`
+ * pthreads: the all-host-cores number of bench.py --impl reference. Per-shard sizes and worker seconds come back. */
+int gooracle_pack_shards_mt(const gotar_entry *es, const size_t *lo, const size_t *hi, size_t nshards, int level,
+                            int nthreads, size_t *tar_bytes, size_t *gz_bytes, double *seconds);
+
 #ifdef __cplusplus
 }
 #endif

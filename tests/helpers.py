@@ -146,6 +146,62 @@ def decode_with_tarfile(stream: bytes):
     return out
 
 
+# ---- large manifests: oracle stream and gunzip as running SHA-256 (nothing is held twice) --------------------
+
+def manifest_entries(man, lo: int, hi: int) -> List[Entry]:
+    """oracle.Entry views of manifest rows [lo, hi) (payloads are numpy slices of the arena, not copies)."""
+    st = man.strtab
+    out = []
+    for i in range(lo, hi):
+        e = man.entries[i]
+        tf = int(e["typeflag"])
+        data = man.arena[int(e["data_off"]): int(e["data_off"]) + int(e["size"])] if tf == ord("0") else b""
+        out.append(Entry(name=st[int(e["name_off"]): int(e["name_off"]) + int(e["name_len"])].tobytes(),
+                         size=int(e["size"]), mtime_sec=int(e["mtime_sec"]), mtime_nsec=int(e["mtime_nsec"]),
+                         mode=int(e["mode"]), uid=int(e["uid"]), gid=int(e["gid"]),
+                         uname=st[int(e["uname_off"]): int(e["uname_off"]) + int(e["uname_len"])].tobytes(),
+                         gname=st[int(e["gname_off"]): int(e["gname_off"]) + int(e["gname_len"])].tobytes(),
+                         typeflag=tf, data=data))
+    return out
+
+
+def oracle_tar_sha256(man, group_bytes: int = 256 << 20, group_entries: int = 20000):
+    """(sha256 hex, length) of the oracle's tar stream for a whole manifest, built group by group."""
+    h = hashlib.sha256()
+    total = 0
+    sizes = man.entries["size"]
+    lo = 0
+    while lo < man.n:
+        hi, acc = lo, 0
+        while hi < man.n and hi - lo < group_entries and (hi == lo or acc + int(sizes[hi]) <= group_bytes):
+            acc += int(sizes[hi])
+            hi += 1
+        total += oracle.tar_stream_update(manifest_entries(man, lo, hi), h.update, trailer=False)
+        lo = hi
+    h.update(bytes(1024))
+    return h.hexdigest(), total + 1024
+
+
+def gunzip_sha256(buf, piece: int = 16 << 20):
+    """(sha256 hex, length, members) of the decompressed content of a (multi-member) gzip buffer, streamed."""
+    import zlib
+    h = hashlib.sha256()
+    mv = memoryview(buf)
+    n, pos, members = 0, 0, 0
+    while pos < len(mv):
+        d = zlib.decompressobj(31)
+        members += 1
+        while not d.eof:
+            if pos >= len(mv):
+                raise ValueError("gzip stream ends inside a member")
+            out = d.decompress(mv[pos:pos + piece])
+            pos += min(piece, len(mv) - pos)
+            h.update(out)
+            n += len(out)
+        pos -= len(d.unused_data)
+    return h.hexdigest(), n, members
+
+
 # ---- SIMT emulator harness (kernel logic on CPU) ------------------------------------------------------------
 
 _EMU = None

@@ -162,3 +162,17 @@ def test_path_clean_matches_go_semantics():
 def test_header_errors(name):
     with pytest.raises(oracle.OracleError):
         oracle.tar_stream(helpers.ERROR_CASES[name])
+
+
+def test_piecewise_oracle_hash_and_streamed_gunzip_agree_with_the_whole_stream():
+    """The helpers the full-size config tests use (tests/test_gpu_configs.py): the oracle stream hashed group by group
+    and a multi-member gzip inflated piece by piece give the SHA-256 of the whole stream."""
+    import gzip
+    import hashlib
+    from devspace_b200 import synth
+    man = synth.tree_c2(400, 1_500_000)
+    sha, n = helpers.oracle_tar_sha256(man, group_bytes=200_000, group_entries=33)
+    ref = oracle.tar_stream(helpers.manifest_entries(man, 0, man.n))
+    assert (sha, n) == (hashlib.sha256(ref).hexdigest(), len(ref))
+    two = gzip.compress(ref[:700_001], 1) + gzip.compress(ref[700_001:], 1)
+    assert helpers.gunzip_sha256(two, piece=65_000) == (sha, n, 2)
