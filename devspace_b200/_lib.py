@@ -21,11 +21,14 @@ SYMBOLS = [
     "dsg_abi_version", "dsg_strerror", "dsg_device_count", "dsg_last_error", "dsg_ctx_create", "dsg_ctx_destroy",
     "dsg_ctx_set_opts",
     "dsg_pinned_alloc", "dsg_pinned_free", "dsg_entry_header_bytes", "dsg_tar_size", "dsg_gzip_bound",
-    "dsg_shard_bounds", "dsg_stitch_members", "dsg_pack", "dsg_pack_tar_only", "dsg_pack_fd", "dsg_pack_device", "dsg_get_stats", "dsg_dev_tar_build",
+    "dsg_shard_bounds", "dsg_crc32_combine", "dsg_stitch_members", "dsg_pack", "dsg_pack_tar_only", "dsg_pack_fd", "dsg_pack_device", "dsg_get_stats", "dsg_dev_tar_build",
     "dsg_dev_crc32", "dsg_dev_deflate", "dsg_dev_gzip", "dsg_dev_alloc", "dsg_dev_free", "dsg_dev_upload",
     "dsg_dev_download", "dsg_crc32_noalloc", "dsg_file_crc32", "dsg_dev_file_crc32", "dsg_directory_hash", "dsg_docker_context_tar", "dsg_walk", "dsg_written_count", "dsg_written_get",
     "dsg_written_entries", "dsg_written_free", "dsg_write_tar",
+    "dsg_multi_create", "dsg_multi_destroy", "dsg_multi_last_error", "dsg_multi_shards", "dsg_multi_get_stats",
+    "dsg_multi_pack_fd", "dsg_multi_pack",
 ]
+DSG_MULTI_ONE_MEMBER = 1
 
 
 class DsgOpts(ctypes.Structure):
@@ -109,5 +112,16 @@ def load(build_if_missing: bool = True):
     lib.dsg_crc32_noalloc.argtypes = [vp, sz, POINTER(c_uint32), c_char_p, sz]
     lib.dsg_file_crc32.argtypes = [vp, vp, sz, vp, sz, vp]
     lib.dsg_dev_file_crc32.argtypes = [vp, vp, sz, vp, sz, vp]
+    lib.dsg_crc32_combine.argtypes = [c_uint32, c_uint32, c_uint64]
+    lib.dsg_crc32_combine.restype = c_uint32
+    lib.dsg_multi_create.argtypes = [POINTER(c_int), c_int, POINTER(DsgOpts), POINTER(vp)]
+    lib.dsg_multi_destroy.argtypes = [vp]
+    lib.dsg_multi_destroy.restype = None
+    lib.dsg_multi_last_error.argtypes = [vp]
+    lib.dsg_multi_last_error.restype = c_char_p
+    lib.dsg_multi_shards.argtypes = [vp]
+    lib.dsg_multi_get_stats.argtypes = [vp, c_int, POINTER(DsgStats)]
+    lib.dsg_multi_pack_fd.argtypes = [vp, vp, sz, vp, sz, vp, sz, c_int, c_uint32, u64p]
+    lib.dsg_multi_pack.argtypes = [vp, vp, sz, vp, sz, vp, sz, c_uint32, vp, sz, POINTER(sz)]
     _lib = lib
     return lib

@@ -120,9 +120,12 @@ static_assert(kMaxDist % 16 == 0 && kLook % 16 == 0, "ring loads move 16-byte gr
 // misc[] slots
 enum { kMTicket = 0, kMStart, kMNTok, kMMode, kMOutLo, kMOutHi, kMHdrBits, kMChunkBytes, kMHlit, kMHdist, kMHclen,
        kMNRle, kMBodyDyn, kMBodyFix, kMError, kMRunCtr /* kTeams slots */, kMRunStart = kMRunCtr + kTeams,
+       kMFlat /* every 8 KiB of the chunk has a flat byte histogram */, kMProbe /* matches found in the first tile of
+       every team */, kMStale /* the window has to be rebuilt before the next chunk */,
        kMScan = 32 /* CTA scan: 32 warp partials + carry; team scans: 20 words each */, kMTeamScan = kMScan,
-       kMTeamScanStride = 20 };
-static_assert(kMRunStart < kMScan && kMTeamScan + kTeams * kMTeamScanStride <= 192, "misc[] slots");
+       kMTeamScanStride = 20, kMBulkBar = 176 /* kTeams mbarriers, 8 bytes each */ };
+static_assert(kMBulkBar % 2 == 0 && kMBulkBar + 2 * kTeams <= 192 && kMBulkBar >= 144, "mbarrier words in misc[]");
+static_assert(kMStale < kMScan && kRun == 8 && kMTeamScan + kTeams * kMTeamScanStride <= 192, "misc[] slots");
 
 // Kernel parameter block
 struct LzParams {
@@ -331,6 +334,76 @@ struct SmemBitWriter {
 };
 
 // ---------------------------------------------------------------------------------------------------------
+// incompressible chunks
+// ---------------------------------------------------------------------------------------------------------
+// Random bytes (compressed or encrypted payloads: archives, images, .gz files inside the tree) used to cost the full
+// search, parse and Huffman work -- 1.04 M cycles per 64 KiB, a third of a text chunk -- only to end as a stored
+// block. A chunk now takes the stored exit early when BOTH hold:
+//   (1) every 8 KiB of it has a flat byte histogram: 2 KiB sampled (16 of every 64 bytes), chi-square against the
+//       uniform distribution below kFlatChi2 (uniform data: 255 +- 23; base64, text, machine code, tables: thousands).
+//       Integer arithmetic only, so the GPU and the emulator decide alike;
+//   (2) the first tile of every team (the first 8 KiB, searched normally against the 32 KiB window) found at most
+//       kFlatMaxMatches matches -- a copy of earlier incompressible bytes (a duplicated image) shows up here.
+// What this gives up: a repeat that begins later than 8 KiB into an all-flat chunk is not used for that chunk.
+// The window is rebuilt from the stream at the next chunk (kMStale), which therefore sees its full dictionary.
+constexpr int kFlatBlock = 8192;
+constexpr int kFlatSampleStride = 64;   // one 16-byte granule of every 64 bytes
+constexpr int kFlatMinSamples = 1024;
+constexpr int kFlatChi2 = 480;          // ten standard deviations above the mean of uniform data
+constexpr int kFlatMaxMatches = 8;
+
+// All threads of the CTA. hist: 32 x 128 words (one u16 histogram per warp). Writes 1 / 0 to *flat. Ends with a barrier.
+DSG_D void chunk_flatness(const uint8_t *in, uint64_t len, int64_t cs, int chunk_len, uint32_t *hist, uint32_t *flat) {
+  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) *flat = ((((uintptr_t)(in + cs)) & 15) == 0 && chunk_len >= kFlatBlock) ? 1u : 0u;
+  __syncthreads();
+  if (*flat == 0u) return;  // uniform
+  uint32_t *h = hist + warp * 128;
+  const int nblocks = (chunk_len + kFlatBlock - 1) / kFlatBlock;
+  for (int b = (int)warp; b < nblocks; b += kLzWarps) {
+    for (uint32_t i = lane; i < 128; i += 32) h[i] = 0;
+    __syncwarp();
+    const int blen = chunk_len - b * kFlatBlock < kFlatBlock ? chunk_len - b * kFlatBlock : kFlatBlock;
+    uint32_t n = 0;
+    for (int o = (int)lane * kFlatSampleStride; o + 16 <= blen; o += 32 * kFlatSampleStride) {
+      const int64_t g = cs + (int64_t)b * kFlatBlock + o;
+      if (g + 16 > (int64_t)len) break;
+#if defined(DSG_EMU)
+      const uint4 v = *reinterpret_cast<const uint4 *>(in + g);
+#else
+      const uint4 v = __ldg(reinterpret_cast<const uint4 *>(in + g));
+#endif
+      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          const uint32_t byte = (w[k] >> (8 * j)) & 0xffu;
+          atomicAdd(&h[byte >> 1], (byte & 1u) ? 0x10000u : 1u);
+        }
+      }
+      n += 16;
+    }
+    __syncwarp();
+    // sum of squared counts, 8 bins per lane
+    uint32_t sq = 0;
+    for (uint32_t i = lane; i < 128; i += 32) {
+      const uint32_t c0 = h[i] & 0xffffu, c1 = h[i] >> 16;
+      sq += c0 * c0 + c1 * c1;
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      sq += __shfl_xor_sync(0xffffffffu, sq, o);
+      n += __shfl_xor_sync(0xffffffffu, n, o);
+    }
+    // chi2 = 256 / n * sum(c^2) - n < kFlatChi2
+    const bool ok = n >= (uint32_t)kFlatMinSamples && 256ull * sq < (uint64_t)n * (n + (uint32_t)kFlatChi2);
+    if (lane == 0 && !ok) atomicAnd(flat, 0u);
+    __syncwarp();
+  }
+  __syncthreads();
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // tile phases
 // ---------------------------------------------------------------------------------------------------------
 
@@ -368,6 +441,77 @@ DSG_D void load_ring(uint8_t *s_data, const LzParams &P, int64_t cs, int rp0, in
       if (slot + 16 <= (uint32_t)(kLook + 48)) *reinterpret_cast<uint4 *>(s_data + kRing + slot) = v;
     }
   }
+}
+
+// ---- bulk staging of a tile: cp.async.bulk (the TMA engine's 1-D copy) + mbarrier ------------------------------------
+// A tile's bytes travel global -> shared memory without passing through registers: ONE thread of the team arms the
+// team's mbarrier with the byte count and issues the copies (a tile is one to two ring pieces plus the mirror of
+// the ring start), the team waits on the mbarrier phase right before it hashes the tile. Source: this GPU's own
+// global memory, no tensor map, no multicast. Needs 16-byte aligned source, destination and sizes: tiles at the
+// edges of the stream (dictionary of the previous segment, zero fill behind the end) take load_ring instead.
+#if !defined(DSG_EMU)
+DSG_D void mbar_init(uint32_t mbar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mbar), "r"(count) : "memory");
+}
+DSG_D void mbar_expect_tx(uint32_t mbar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+}
+DSG_D void mbar_wait(uint32_t mbar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(mbar),
+      "r"(parity)
+      : "memory");
+}
+DSG_D void bulk_g2s(uint32_t dst_smem, const void *src, uint32_t bytes, uint32_t mbar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_smem),
+               "l"(src), "r"(bytes), "r"(mbar)
+               : "memory");
+}
+#endif
+
+// True when the positions [rp0, rp1) of the run can be staged by bulk copies.
+DSG_D bool bulk_ok(const LzParams &P, int64_t cs, int rp0, int rp1) {
+#if defined(DSG_EMU)
+  (void)P; (void)cs; (void)rp0; (void)rp1;
+  return false;
+#else
+  const int64_t g0 = cs + rp0, g1 = cs + rp1;
+  return g0 >= 0 && g1 <= (int64_t)P.len && ((((uintptr_t)P.in) | (uint64_t)g0 | (uint64_t)g1) & 15) == 0;
+#endif
+}
+
+// One thread: arms `mbar` and issues the copies of stream bytes [cs + rp0, cs + rp1) to their ring slots (and to the
+// mirror behind the ring end). rp0, rp1 multiples of 16, rp1 - rp0 <= kRing.
+DSG_D void bulk_load_ring(uint8_t *s_data, const LzParams &P, int64_t cs, int rp0, int rp1, uint32_t mbar) {
+#if !defined(DSG_EMU)
+  const uint32_t base = (uint32_t)__cvta_generic_to_shared(s_data);
+  const uint8_t *src = P.in + cs + rp0;
+  const uint32_t n = (uint32_t)(rp1 - rp0);
+  const uint32_t s0 = ring_slot(rp0);
+  const uint32_t first = s0 + n <= (uint32_t)kRing ? n : (uint32_t)kRing - s0;  // piece up to the ring end
+  const uint32_t mir = (uint32_t)(kLook + 48);
+  // mirror parts: slots [0, mir) of either piece
+  const uint32_t m1 = s0 < mir ? (s0 + first < mir ? first : mir - s0) : 0u;    // of the first piece (starts at s0)
+  const uint32_t m2 = n - first < mir ? n - first : mir;                        // of the wrapped piece (starts at 0)
+  // generic-proxy accesses of these slots (older laps) are ordered before the async-proxy writes
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  mbar_expect_tx(mbar, n + m1 + m2);
+  bulk_g2s(base + s0, src, first, mbar);
+  if (m1) bulk_g2s(base + (uint32_t)kRing + s0, src, m1, mbar);
+  if (n > first) {
+    bulk_g2s(base, src + first, n - first, mbar);
+    bulk_g2s(base + (uint32_t)kRing, src + first, m2, mbar);
+  }
+#else
+  (void)s_data; (void)P; (void)cs; (void)rp0; (void)rp1; (void)mbar;
+#endif
 }
 
 // Inserts positions [rp0, rp1) into the hash chains in EXACT stream order (nearest candidate first), 1024
@@ -1084,6 +1228,19 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
   uint32_t *t_scan = s_misc + kMTeamScan + team * kMTeamScanStride;
   uint32_t *t_ctr = s_misc + kMRunCtr + team;
 
+  // one mbarrier per team for the bulk staging of its tiles (8-byte words behind the scan scratch of s_misc)
+  uint32_t bulk_phase = 0;  // parity of the team's next mbarrier phase (uniform inside the team)
+#if !defined(DSG_EMU)
+  const uint32_t t_mbar = (uint32_t)__cvta_generic_to_shared(s_misc + kMBulkBar + 2 * team);
+  if (tid == 0) {
+    for (int i = 0; i < kTeams; i++) mbar_init((uint32_t)__cvta_generic_to_shared(s_misc + kMBulkBar + 2 * i), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+#else
+  const uint32_t t_mbar = 0;
+#endif
+
   long long t_last = 0;
 #define LZ_PROF(k)                                                    \
   do {                                                                \
@@ -1112,17 +1269,9 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
     const int chunk = (int)lz_chunk_size(c0, P.chunk_bytes, nbig * R);  // a run has chunks of one size
     const int64_t rs = (int64_t)lz_chunk_offset(c0, P.chunk_bytes, nbig * R);  // stream offset of the run
     const int64_t avail = rs + (P.dict ? (int64_t)P.dict_len : 0);
-    const int lo_rp = -(int)(avail < (int64_t)kMaxDist ? avail : (int64_t)kMaxDist);
-    for (uint32_t i = tid; i < (uint32_t)kHashSize; i += kLzThreads) s_head[i] = kNil;
-    // dictionary + first tile + look-ahead are resident before the dictionary is hashed (the last three
-    // dictionary positions hash over the first bytes of the run). kMaxDist is a multiple of 16.
+    int lo_rp = -(int)(avail < (int64_t)kMaxDist ? avail : (int64_t)kMaxDist);
     const LzGroup g_all{(int)tid, kLzThreads, 0};
-    load_ring(s_data, P, rs, -(((-lo_rp) + 15) & ~15), kTile + kLook, g_all);
-    __syncthreads();
-    if (tid == 0) s_misc[kMRunStart] = 0;
-    __syncthreads();
-    insert_positions(s_data, s_prev, s_head, lo_rp, 0, lo_rp, g_all, s_misc + kMScan, &s_misc[kMRunStart]);
-    LZ_PROF(kProfLoad);
+    if (tid == 0) s_misc[kMStale] = 1;  // a run starts by building its window
 
     for (uint32_t k = 0; k < rlen; k++) {
     const uint32_t c = c0 + k;
@@ -1131,12 +1280,30 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
     const int crp = (int)k * chunk;  // run-relative position of the chunk start
     const int chunk_len = (int)((int64_t)P.len - cs < chunk ? (int64_t)P.len - cs : chunk);
     __syncthreads();
+    if (s_misc[kMStale]) {
+      // The window: at the start of a run, and again behind a chunk that took the stored exit (its tiles were not
+      // loaded). Dictionary + first tile + look-ahead are resident before the dictionary is hashed (the last three
+      // dictionary positions hash over the first bytes of the chunk). kMaxDist and crp are multiples of 16.
+      if (crp > 0) lo_rp = crp - kMaxDist;
+      for (uint32_t i = tid; i < (uint32_t)kHashSize; i += kLzThreads) s_head[i] = kNil;
+      load_ring(s_data, P, rs, crp - (((crp - lo_rp) + 15) & ~15), crp + kTile + kLook, g_all);
+      __syncthreads();
+      if (tid == 0) {
+        s_misc[kMRunStart] = 0;
+        s_misc[kMStale] = 0;
+      }
+      __syncthreads();
+      insert_positions(s_data, s_prev, s_head, lo_rp, crp, lo_rp, g_all, s_misc + kMScan, &s_misc[kMRunStart]);
+      LZ_PROF(kProfLoad);
+    }
     for (uint32_t i = tid; i < 288; i += kLzThreads) s_lfreq[i] = 0;
     if (tid < 32) s_dfreq[tid] = 0;
     if (tid == 0) {
       s_misc[kMStart] = 0;
       s_misc[kMNTok] = 0;
+      s_misc[kMProbe] = 0;
     }
+    chunk_flatness(P.in, P.len, cs, chunk_len, reinterpret_cast<uint32_t *>(s_work), &s_misc[kMFlat]);  // barriers inside
     __syncthreads();
 
     // ---- tiles: a two-stage pipeline over two teams -----------------------------------------------------------
@@ -1148,15 +1315,34 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
     // one tile in flight) are filled with the other team's work. The ring holds the 32 KiB window plus both tiles:
     // loading tile t+1 overwrites only bytes that lie beyond the window of every position of tile t.
     const int ntiles = (chunk_len + kTile - 1) / kTile;
+    // every team has a first tile, so the CTA-wide barrier behind it is reached by all threads
+    const bool flat_candidate = s_misc[kMFlat] != 0u && ntiles >= kTeams;
+    bool stored_exit = false;
     for (int t = (int)team; t < ntiles; t += kTeams) {
       const int tile_rp = crp + t * kTile;
       const int tile_len = chunk_len - t * kTile < kTile ? chunk_len - t * kTile : kTile;
       const bool has_next = t + 1 < ntiles;
       // -- stage A
+      // The tile's bytes + look-ahead replace the oldest ring bytes: those lie beyond the window of every tile that is
+      // still being searched (the nearest one, tile t-3, reaches back exactly to the first byte that is kept), so the
+      // copy does not have to wait for the hashing of tile t-1 and overlaps that wait. (The first tile of a window came
+      // with the dictionary; it is loaded again, the same bytes.)
+      const bool staged = tile_rp > 0;
+      const bool bulk = staged && bulk_ok(P, rs, tile_rp + kLook, tile_rp + kTile + kLook);
+      if (bulk) {
+        if (g_team.tid == 0) bulk_load_ring(s_data, P, rs, tile_rp + kLook, tile_rp + kTile + kLook, t_mbar);
+      } else if (staged) {
+        load_ring(s_data, P, rs, tile_rp + kLook, tile_rp + kTile + kLook, g_team);
+      }
+      LZ_PROF(kProfLoad);
       if (t > 0) handoff_wait(kBarInsert + (int)prev_team);  // tile t-1 is in the chains
       LZ_PROF(kProfWaitA);
-      if (tile_rp > 0) {  // (the first tile of a run came with the dictionary) its bytes + look-ahead replace the oldest
-        load_ring(s_data, P, rs, tile_rp + kLook, tile_rp + kTile + kLook, g_team);
+      if (bulk) {
+#if !defined(DSG_EMU)
+        mbar_wait(t_mbar, bulk_phase);
+#endif
+        bulk_phase ^= 1u;
+      } else if (staged) {
         group_sync(g_team);
       }
       LZ_PROF(kProfLoad);
@@ -1173,6 +1359,23 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
         atomicAdd(&P.prof[kProfWarpSearch], (unsigned long long)(clock64() - t_ws) / kTeamWarps);
       group_sync(g_team);
       LZ_PROF(kProfSearch);
+      if (flat_candidate && t == (int)team) {
+        // condition (2) of the stored exit: what the shallow search found in the first tile of every team
+        const uint2 m8 = *reinterpret_cast<const uint2 *>(t_mlen + g_team.tid * kRun);  // kRun == 8 positions
+        uint32_t found = 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) found += (((m8.x >> (8 * j)) & 0xffu) ? 1u : 0u) + (((m8.y >> (8 * j)) & 0xffu) ? 1u : 0u);
+        if (g_team.tid * kRun >= tile_len) found = 0;
+        for (int o = 16; o > 0; o >>= 1) found += __shfl_xor_sync(0xffffffffu, found, o);
+        if (lane == 0 && found) atomicAdd(&s_misc[kMProbe], found);
+        __syncthreads();
+        if (s_misc[kMProbe] <= (uint32_t)kFlatMaxMatches) {
+          // The chunk is stored. Team 3's hand-off for tile 4 is the one arrival nobody has consumed yet.
+          if (team == 0 && ntiles > kTeams) handoff_wait(kBarInsert + kTeams - 1);
+          stored_exit = true;
+          break;
+        }
+      }
       // -- stage B: the refine rounds parse from the tile start (the true first token start is not known before tile
       // t-1 has been parsed for good; a parse from a wrong start joins the true one within a few tokens, and this
       // way the choice of deep-searched positions does not depend on timing)
@@ -1233,6 +1436,14 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
     }
     __syncthreads();
     LZ_PROF(kProfJoin);
+    if (stored_exit) {  // uniform: decided from shared memory behind a CTA-wide barrier
+      if (tid == 0) {
+        const uint32_t n_stored_blocks = ((uint32_t)chunk_len + kStoredMax - 1) / kStoredMax;
+        P.chunk_meta[c] = (((uint32_t)chunk_len + 5 * n_stored_blocks) << 1) | 1u;  // the gather kernel copies the input
+        s_misc[kMStale] = 1;
+      }
+      continue;  // the next chunk starts with a barrier
+    }
 
     // ---- Huffman tables and exact sizes ------------------------------------------------------------------
     if (tid == 0) {

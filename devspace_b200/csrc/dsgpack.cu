@@ -680,6 +680,8 @@ int dsg_stitch_members(const uint8_t *const *members, const size_t *member_lens,
   return DSG_OK;
 }
 
+uint32_t dsg_crc32_combine(uint32_t crc_a, uint32_t crc_b, uint64_t len_b) { return crc_combine(crc_a, crc_b, len_b); }
+
 int dsg_shard_bounds(const dsg_entry *entries, size_t n, const char *strtab, size_t strtab_len, int nshards,
                      uint64_t *bounds) {
   if ((!entries && n) || !strtab || !bounds || nshards <= 0) return DSG_E_ARG;

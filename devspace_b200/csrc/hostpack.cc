@@ -28,6 +28,7 @@
 #include <map>
 #include <string>
 #include <thread>
+#include <unordered_map>
 #include <vector>
 
 #include "../../include/dsgpack.h"
@@ -57,10 +58,27 @@ std::string join(const std::string &a, const std::string &b) {
 
 int64_t round_mtime(const struct timespec &ts) { return (int64_t)ts.tv_sec + (ts.tv_nsec >= 500000000L ? 1 : 0); }
 
-const dsg_file_info *lookup(const dsg_sync_config *cfg, const std::string &name) {
+// fileIndex.fileMap (file_index.go:8-11) is a Go map: the index handed in as an array is hashed once per walk (a
+// 100 k-file tree with a 100 k-entry index was 10^10 string compares as a linear scan). The first entry of a name wins,
+// as in the scan it replaces.
+struct FileMapIndex {
+  const dsg_sync_config *cfg = nullptr;
+  std::unordered_map<std::string, const dsg_file_info *> by_name;
+};
+thread_local FileMapIndex g_index;
+
+void index_file_map(const dsg_sync_config *cfg) {
+  g_index.cfg = cfg;
+  g_index.by_name.clear();
+  g_index.by_name.reserve(cfg->file_map_len * 2 + 1);
   for (size_t i = 0; i < cfg->file_map_len; i++)
-    if (name == cfg->file_map[i].name) return &cfg->file_map[i];
-  return nullptr;
+    if (cfg->file_map[i].name) g_index.by_name.emplace(cfg->file_map[i].name, &cfg->file_map[i]);
+}
+
+const dsg_file_info *lookup(const dsg_sync_config *cfg, const std::string &name) {
+  if (g_index.cfg != cfg) index_file_map(cfg);
+  auto it = g_index.by_name.find(name);
+  return it == g_index.by_name.end() ? nullptr : it->second;
 }
 
 uint32_t intern(Walked &w, const std::string &s) {
@@ -245,7 +263,10 @@ extern "C" {
 int dsg_walk(const dsg_file_info *files, size_t nfiles, const dsg_sync_config *cfg, dsg_written **out) {
   if (!cfg || !cfg->watch_path || !out || (nfiles && !files)) return DSG_E_ARG;
   dsg_written *h = new dsg_written();
+  index_file_map(cfg);  // once per walk: the caller may have changed the index since the last one
   int rc = walk_all(h->w, files, nfiles, cfg);
+  g_index.cfg = nullptr;
+  g_index.by_name.clear();
   if (rc) {
     delete h;
     return rc;

@@ -157,6 +157,11 @@ uint64_t dsg_gzip_bound(uint64_t tar_bytes);
 int dsg_stitch_members(const uint8_t *const *members, const size_t *member_lens, const uint64_t *tar_lens, size_t n,
                        uint8_t *out, size_t out_cap, size_t *out_len);
 
+/* CRC32-IEEE of A || B from crc(A), crc(B) and len(B) (x^(8 len_b) mod P): what a caller that concatenates the
+ * shards' members itself needs for a single trailer. Host integer work; hash/crc32 has no such function, the Go
+ * side would otherwise have to re-read the stream. */
+uint32_t dsg_crc32_combine(uint32_t crc_a, uint32_t crc_b, uint64_t len_b);
+
 /* Contiguous entry ranges balanced by tar-stream bytes for `nshards` GPUs:
  * shard s owns entries [bounds[s], bounds[s+1]). `bounds` has nshards+1 slots. Files are never split. */
 int dsg_shard_bounds(const dsg_entry *entries, size_t n, const char *strtab, size_t strtab_len, int nshards,
@@ -192,6 +197,28 @@ int dsg_pack_device(dsg_ctx *ctx, const dsg_entry *d_entries, size_t n, const ch
 
 /* Counters of the most recent dsg_pack* call on this context. */
 int dsg_get_stats(const dsg_ctx *ctx, dsg_stats *out);
+
+/* ---- one call, several GPUs, one ordered archive (devspace_b200/csrc/multipack.cu) ------------------------------ *
+ * Replaces the same lines as dsg_pack -- ONE writeTar call per archive from one goroutine (upstream.go:342; kaniko's
+ * whole tree, util.go:68-73) -- on a box with several GPUs: the header list is cut into ndev
+ * contiguous ranges balanced by tar-stream bytes (dsg_shard_bounds), device devices[s] packs range s on a host thread
+ * of its own, and the calling thread writes the members in shard order to `fd` (or `out`) while later shards are
+ * still being packed. mode 0: the members back to back, a multi-member .tar.gz (GNU gzip/tar, CPython read it as one
+ * stream); DSG_MULTI_ONE_MEMBER: stitched into a single member on the fly (for decoders that stop after the first
+ * member). The same device may be listed more than once (several contexts on one GPU). Every shard's member is
+ * staged in a pinned buffer of its context until its turn to be written. No CPU fallback: dsg_multi_create fails
+ * with DSG_E_CUDA when a listed device is missing. */
+typedef struct dsg_multi dsg_multi; /* opaque */
+#define DSG_MULTI_ONE_MEMBER 1u
+int dsg_multi_create(const int *devices, int ndev, const dsg_opts *opts, dsg_multi **out);
+void dsg_multi_destroy(dsg_multi *m);
+const char *dsg_multi_last_error(const dsg_multi *m);
+int dsg_multi_shards(const dsg_multi *m);
+int dsg_multi_get_stats(const dsg_multi *m, int shard, dsg_stats *out);   /* of the most recent call */
+int dsg_multi_pack_fd(dsg_multi *m, const dsg_entry *entries, size_t n, const char *strtab, size_t strtab_len,
+                      const uint8_t *arena, size_t arena_len, int fd, uint32_t mode, uint64_t *out_len);
+int dsg_multi_pack(dsg_multi *m, const dsg_entry *entries, size_t n, const char *strtab, size_t strtab_len,
+                   const uint8_t *arena, size_t arena_len, uint32_t mode, uint8_t *out, size_t out_cap, size_t *out_len);
 
 /* ---- host mirror of the Go call site (devspace_b200/csrc/hostpack.cc; host code only: walk, stat, read) ------ */
 

@@ -138,3 +138,27 @@ def test_emulated_deflate_under_other_thread_schedules(sched):
     for line in r.stdout.strip().split("\n")[:-1]:
         name, digest = line.split()
         assert hashlib.sha256(emu_deflate(CASES[name], grid=2, run_chunks=2)).hexdigest() == digest, (sched, name)
+
+
+def test_emulated_stored_exit_keeps_the_window_and_sees_copies():
+    """Chunks of flat bytes leave through the stored exit after their first tiles; the chunk behind one rebuilds its
+    window from the stream, and a copy of earlier random bytes (visible in the first tiles) still compresses."""
+    rnd = helpers.rng_bytes(21, 65_536 * 2)
+    text = realistic_text(40_000, 22)
+    # random chunk, random chunk, then text whose first 32 KiB repeat the text that precedes the random bytes
+    data = text[:32_768] + rnd[: 65_536 * 2 - 32_768] + text[:32_768] + text[32_768:]
+    for rc in (1, 3):
+        z = emu_deflate(data, run_chunks=rc, grid=1)
+        assert zlib.decompress(z, -15) == data
+    # a duplicated random block: the second copy starts a chunk, so its first tiles match the window -> not stored
+    blk = helpers.rng_bytes(23, 20_000)
+    dup = helpers.rng_bytes(24, 65_536 - 20_000) + blk + blk + helpers.rng_bytes(25, 30_000)
+    z = emu_deflate(dup, run_chunks=2, grid=1)
+    assert zlib.decompress(z, -15) == dup
+    assert len(z) < len(dup) - 15_000                 # the second copy costs (almost) nothing
+    # text right behind a stored chunk in the same run still uses matches into that chunk's tail (rebuilt window)
+    tail = text[:20_000]
+    mix = helpers.rng_bytes(26, 65_536 - 20_000) + tail + tail + realistic_text(30_000, 27)
+    z = emu_deflate(mix, run_chunks=2, grid=1)
+    assert zlib.decompress(z, -15) == mix
+    assert len(z) < 65_536 + 5 * 2 + 0.45 * 50_000
