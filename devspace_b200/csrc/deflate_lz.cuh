@@ -72,6 +72,7 @@ constexpr uint32_t kTokMatch = 0x80000000u;
 // block with one pair of Huffman tables, and its epilogue (tree construction, sizes, bit packing, the drain of the
 // tile pipeline) is the part of the kernel in which most threads wait -- large inputs amortise it over more bytes.
 constexpr int kMaxChunk = 4 * kChunk;
+constexpr int kMinChunk = kChunk / 4;  // small inputs: 16 / 32 KiB chunks (the host decides, dsgpack.cu lz_geometry)
 constexpr int kTokSlotWords = kMaxChunk + 64;  // per-CTA token scratch (u32), worst case all literals + EOB
 DSG_HD uint32_t lz_slot_bytes(uint32_t chunk_bytes) { return chunk_bytes + 128; }  // per-chunk output slot (16-byte aligned)
 // The first big_chunks chunks of a launch have chunk_bytes bytes (they are handed out in runs), the chunks behind
@@ -84,9 +85,9 @@ DSG_HD uint32_t lz_chunk_size(uint32_t c, uint32_t chunk_bytes, uint32_t big_chu
   return c < big_chunks ? chunk_bytes : (uint32_t)kChunk;
 }
 
-// Upper bound of the raw deflate output for n input bytes: a chunk never exceeds its stored encoding
-// (two stored blocks for a 64 KiB chunk), plus the 2-byte terminator.
-DSG_HD uint64_t lz_deflate_bound(uint64_t n) { return n + 10 * ((n + kChunk - 1) / kChunk) + 2 + 64; }
+// Upper bound of the raw deflate output for n input bytes: a chunk never exceeds its stored encoding (one stored
+// block for a 16 KiB chunk, two for a 64 KiB one: at most 10 bytes per 16 KiB), plus the 2-byte terminator.
+DSG_HD uint64_t lz_deflate_bound(uint64_t n) { return n + 10 * ((n + kMinChunk - 1) / kMinChunk) + 2 + 64; }
 
 // Shared-memory carve-up (dynamic shared memory; byte offsets, 16-byte aligned)
 struct LzLayout {

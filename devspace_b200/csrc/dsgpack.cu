@@ -161,9 +161,10 @@ int begin_call(dsg_ctx *ctx) {
 
 // ---- stage: archive/tar Writer ---------------------------------------------------------------------------
 
-// Runs the plan kernels and returns T (synchronises once to read it and the status word).
-int tar_plan(dsg_ctx *ctx, const dsg_entry *d_entries, uint32_t n, const char *d_strtab, uint64_t strtab_len,
-             uint64_t arena_len, uint32_t flags, uint64_t *tar_len, uint64_t *payload) {
+// Enqueues the plan kernels (no synchronisation): per-entry stream offsets in ent_off, totals and the status word in
+// `scalars` on the device.
+int tar_plan_enqueue(dsg_ctx *ctx, const dsg_entry *d_entries, uint32_t n, const char *d_strtab, uint64_t strtab_len,
+                     uint64_t arena_len) {
   const uint32_t ncta = (n + kPlanThreads - 1) / kPlanThreads;
   CU(ctx->ent_blocks.ensure(sizeof(uint64_t) * (size_t)(n + 1)));
   CU(ctx->cta_sums.ensure(sizeof(uint64_t) * (size_t)(ncta + 1)));
@@ -188,6 +189,15 @@ int tar_plan(dsg_ctx *ctx, const dsg_entry *d_entries, uint32_t n, const char *d
     CU(cudaMemsetAsync(ctx->ent_off.p, 0, sizeof(uint64_t), ctx->stream));
   }
   toc(ctx, kTimPlan);
+  return DSG_OK;
+}
+
+// Runs the plan kernels and returns T (synchronises once to read it and the status word).
+int tar_plan(dsg_ctx *ctx, const dsg_entry *d_entries, uint32_t n, const char *d_strtab, uint64_t strtab_len,
+             uint64_t arena_len, uint32_t flags, uint64_t *tar_len, uint64_t *payload) {
+  int rc = tar_plan_enqueue(ctx, d_entries, n, d_strtab, strtab_len, arena_len);
+  if (rc) return rc;
+  uint64_t *sc = ctx->scalars.as<uint64_t>();
   CU(cudaMemcpyAsync(ctx->h_scalars, sc, sizeof(uint64_t) * kScalarWords, cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
   DevStatus st;
@@ -330,6 +340,12 @@ bool lz_geometry(const dsg_ctx *ctx, uint64_t len, LzGeometry &G) {
   // Chunk size: the largest of 64 / 128 / 256 KiB that still leaves every SM eight chunks (see kMaxChunk).
   uint32_t chunk_bytes = kChunk;
   while (chunk_bytes < (uint32_t)kMaxChunk && len / (2ull * chunk_bytes) >= 8ull * (uint64_t)ctx->sm_count) chunk_bytes *= 2;
+  // Small inputs: a call lasts as long as its slowest SM, i.e. a whole number of chunk times (1.2 ms per 64 KiB chunk).
+  // With fewer 64 KiB chunks than SMs the chunks shrink to 32 KiB (measured on the B200: +0.4 % output on token-like
+  // text, each chunk carries its own Huffman tables and sync marker; a 4 MB tree 73 x -> 110 x the CPU path), below
+  // 128 KiB -- a change set of a few files, where the call is latency and 2 % of the output is a few hundred bytes --
+  // to 16 KiB. Above that more, smaller chunks only add dictionary builds (16 MB: slower with 32 KiB chunks).
+  if (len < (uint64_t)kChunk * (uint64_t)ctx->sm_count) chunk_bytes = len <= (128u << 10) ? kMinChunk : 2 * kMinChunk;
   if (o.lz_chunk_units == 1 || o.lz_chunk_units == 2 || o.lz_chunk_units == 4) chunk_bytes = o.lz_chunk_units * kChunk;
   // Runs of run_chunks big chunks first (long runs amortise hashing the dictionary); the last half run per SM is cut
   // into 64 KiB chunks and handed out one by one, so that the CTAs finish within a millisecond of each other.
@@ -339,6 +355,10 @@ bool lz_geometry(const dsg_ctx *ctx, uint64_t len, LzGeometry &G) {
   uint64_t tail_bytes = run_chunks > 1 || chunk_bytes > (uint32_t)kChunk
                             ? std::min<uint64_t>(len, (uint64_t)ctx->sm_count * run_chunks * chunk_bytes / 2)
                             : len;
+  if (chunk_bytes < (uint32_t)kChunk) {  // every full chunk is a "big" one; the remainder is one (short) tail chunk
+    run_chunks = 1;
+    tail_bytes = 0;
+  }
   if (o.lz_flags & DSG_LZ_TAIL_SET) tail_bytes = std::min<uint64_t>(len, o.lz_tail_bytes);
   const uint64_t big_runs64 = (len - tail_bytes) / ((uint64_t)run_chunks * chunk_bytes);
   const uint64_t big_chunks64 = big_runs64 * run_chunks;
@@ -1288,6 +1308,90 @@ static int pack_host_pipelined(dsg_ctx *ctx, const dsg_entry *entries, size_t n,
   return DSG_OK;
 }
 
+// Small archives -- the change sets of the dev loop (upstream.go:136: batches of up to 1000 files every 600 ms;
+// BASELINE config 1 is 5 files / 93 KB) -- are bound by launch and synchronisation latency, not by bandwidth: the
+// pipelined path synchronises four times (plan read-back, segment ranges, per-segment sizes, trailer). Here the stream
+// length comes from the host-side plan (pure integer work on the manifest), everything is enqueued on one stream --
+// copy in, plan, layout, CRC, deflate, frame, copy out of the bound -- and the host synchronises ONCE.
+constexpr uint64_t kSmallPathBytes = 4ull << 20;
+
+static int pack_host_small(dsg_ctx *ctx, const dsg_entry *entries, size_t n, const char *strtab, size_t strtab_len,
+                           const uint8_t *arena, size_t arena_len, bool gzip, uint8_t *out, size_t out_cap,
+                           size_t *out_len, uint64_t T) {
+  cudaStream_t st = ctx->stream;
+  CU(cudaEventRecord(ctx->tim[kTimTotal].a, st));
+  // the arena range this manifest touches (a shard of a larger arena copies only its own bytes)
+  uint64_t a_lo = ~0ull, a_hi = 0, P = 0;
+  for (size_t i = 0; i < n; i++) {
+    if (entries[i].typeflag != '0' || entries[i].size <= 0) continue;
+    const uint64_t lo = entries[i].data_off, sz = (uint64_t)entries[i].size;
+    if (lo > arena_len || sz > arena_len - lo) return fail(ctx, DSG_E_RANGE, "entry %zu: %s", i, dsg_strerror(DSG_E_RANGE));
+    a_lo = std::min(a_lo, lo);
+    a_hi = std::max(a_hi, lo + sz);
+    P += sz;
+  }
+  if (a_hi <= a_lo || a_lo == ~0ull) a_lo = a_hi = 0;
+  a_lo &= ~uint64_t(15);
+  const uint64_t bound = gzip ? 18 + lz_deflate_bound(T) : T;
+  CU(ctx->d_entries.ensure(sizeof(dsg_entry) * std::max<size_t>(n, 1)));
+  CU(ctx->d_strtab.ensure(std::max<size_t>(strtab_len, 1)));
+  CU(ctx->d_arena.ensure(a_hi - a_lo + 64));
+  CU(ctx->d_tar.ensure(T + 64));
+  if (gzip) CU(ctx->d_out.ensure(bound + 64));
+  if (n) CU(cudaMemcpyAsync(ctx->d_entries.p, entries, sizeof(dsg_entry) * n, cudaMemcpyHostToDevice, st));
+  if (strtab_len) CU(cudaMemcpyAsync(ctx->d_strtab.p, strtab, strtab_len, cudaMemcpyHostToDevice, st));
+  if (a_hi > a_lo) CU(cudaMemcpyAsync(ctx->d_arena.p, arena + a_lo, a_hi - a_lo, cudaMemcpyHostToDevice, st));
+  const dsg_entry *d_entries = ctx->d_entries.as<dsg_entry>();
+  const char *d_strtab = ctx->d_strtab.as<char>();
+  int rc = tar_plan_enqueue(ctx, d_entries, (uint32_t)n, d_strtab, strtab_len, arena_len);
+  if (rc) return rc;
+  uint8_t *d_tar = ctx->d_tar.as<uint8_t>();
+  tic(ctx, kTimTar);
+  if ((rc = tar_layout(ctx, d_entries, (uint32_t)n, d_strtab, ctx->d_arena.as<uint8_t>(), a_lo, d_tar, 0, T))) return rc;
+  toc(ctx, kTimTar);
+  uint64_t *sc = ctx->scalars.as<uint64_t>();
+  uint64_t copied = T;
+  if (gzip) {
+    uint8_t *d_out = ctx->d_out.as<uint8_t>();
+    if ((rc = crc_reset(ctx))) return rc;
+    CU(cudaMemsetAsync(sc + kSSpare, 0, sizeof(uint64_t), st));
+    tic(ctx, kTimCrc);
+    if ((rc = crc_update(ctx, d_tar, T))) return rc;
+    toc(ctx, kTimCrc);
+    uint64_t dn = 0;
+    if ((rc = deflate_run(ctx, d_tar, T, ctx->opts.level, d_out + 10, bound - 18, &dn))) return rc;
+    gzip_frame_kernel<<<1, 32, 0, st>>>(d_out, bound, sc + kSDeflateBytes, reinterpret_cast<uint32_t *>(sc + kSCrc),
+                                        reinterpret_cast<uint32_t *>(sc + kSSpare));
+    LAUNCH_CHECK();
+    copied = std::min<uint64_t>(out_cap, bound);
+    if (copied) CU(cudaMemcpyAsync(out, d_out, copied, cudaMemcpyDeviceToHost, st));
+  } else {
+    copied = std::min<uint64_t>(out_cap, T);
+    if (copied) CU(cudaMemcpyAsync(out, d_tar, copied, cudaMemcpyDeviceToHost, st));
+  }
+  CU(cudaMemcpyAsync(ctx->h_scalars, sc, sizeof(uint64_t) * kScalarWords, cudaMemcpyDeviceToHost, st));
+  CU(cudaEventRecord(ctx->tim[kTimTotal].b, st));
+  ctx->tim[kTimTotal].used = true;
+  CU(cudaStreamSynchronize(st));  // the one synchronisation of the call
+  DevStatus dst;
+  memcpy(&dst, &ctx->h_scalars[kSStatus], sizeof dst);
+  if (dst.code != 0) return fail(ctx, dst.code, "entry %u: %s", dst.entry, dsg_strerror(dst.code));
+  const uint64_t produced = gzip ? ctx->h_scalars[kSDeflateBytes] + 18 : T;
+  *out_len = (size_t)produced;
+  ctx->stats.entries = n;
+  ctx->stats.payload_bytes = P;
+  ctx->stats.tar_bytes = T;
+  ctx->stats.h2d_bytes = sizeof(dsg_entry) * n + strtab_len + (a_hi - a_lo);
+  ctx->stats.d2h_bytes = copied;
+  ctx->stats.segments = 1;
+  if (gzip) ctx->stats.crc32 = (uint32_t)ctx->h_scalars[kSCrc];
+  finish_stats(ctx, produced);
+  if (produced > out_cap)
+    return fail(ctx, DSG_E_CAPACITY, "output needs %llu bytes, capacity %llu", (unsigned long long)produced,
+                (unsigned long long)out_cap);
+  return DSG_OK;
+}
+
 static int pack_host(dsg_ctx *ctx, const dsg_entry *entries, size_t n, const char *strtab, size_t strtab_len,
                      const uint8_t *arena, size_t arena_len, bool gzip, uint8_t *out, size_t out_cap, size_t *out_len) {
   if (!ctx || !out_len || !out || (n && (!entries || !strtab)) || (arena_len && !arena) || n > 0xfffffff0ull)
@@ -1295,6 +1399,11 @@ static int pack_host(dsg_ctx *ctx, const dsg_entry *entries, size_t n, const cha
   std::lock_guard<std::mutex> g(ctx->mu);
   int rc = begin_call(ctx);
   if (rc) return rc;
+  if (ctx->opts.segment_bytes == 0 && n <= 4096) {  // (a forced segment size asks for the pipelined path)
+    uint64_t T = 0;
+    if (dsg_tar_size(entries, n, strtab, strtab_len, ctx->opts.flags, &T) == DSG_OK && T <= kSmallPathBytes)
+      return pack_host_small(ctx, entries, n, strtab, strtab_len, arena, arena_len, gzip, out, out_cap, out_len, T);
+  }
   return pack_host_pipelined(ctx, entries, n, strtab, strtab_len, arena, arena_len, gzip, out, out_cap, out_len);
 }
 

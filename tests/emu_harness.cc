@@ -69,11 +69,17 @@ int emu_lz_deflate(const uint8_t *in, uint64_t len, const uint8_t *dict, uint32_
     *out_len = 2;
     return 0;
   }
-  // bits 16.. of run_chunks: chunk size in units of 64 KiB (0 = 1), as the host picks it for large inputs
-  uint32_t units = run_chunks >> 16;
+  // bits 16..23 of run_chunks: chunk size in units of 64 KiB (0 = 1), as the host picks it for large inputs;
+  // bits 24.. : chunk size in units of 16 KiB (1 or 2), as the host picks it for small inputs (run_chunks = 1 then)
+  uint32_t units = (run_chunks >> 16) & 0xffu;
+  const uint32_t quarters = run_chunks >> 24;
   run_chunks &= 0xffffu;
   if (units != 2 && units != 4) units = 1;
-  const uint32_t chunk_bytes = units * (uint32_t)kChunk;
+  uint32_t chunk_bytes = units * (uint32_t)kChunk;
+  if (quarters == 1 || quarters == 2) {
+    chunk_bytes = quarters * (uint32_t)kMinChunk;
+    run_chunks = 1;
+  }
   if (run_chunks == 0) run_chunks = 1;
   // as many whole runs of big chunks as fit, the remainder in 64 KiB chunks one by one (the host's DSG_LZ_TAIL=0)
   const uint32_t big_runs = (uint32_t)(len / ((uint64_t)run_chunks * chunk_bytes));

@@ -21,17 +21,18 @@ def _lib():
     return lib
 
 
-def emu_deflate(data: bytes, grid: int = 0, dict_: bytes = b"", run_chunks: int = 1, chunk_units: int = 1):
+def emu_deflate(data: bytes, grid: int = 0, dict_: bytes = b"", run_chunks: int = 1, chunk_units: int = 1,
+                small_chunk_kib: int = 0):
     L = _lib()
     a = np.frombuffer(data, np.uint8)
     d = np.frombuffer(dict_, np.uint8)
-    cap = len(data) + 10 * ((len(data) + 65535) // 65536) + 128
+    cap = len(data) + 10 * ((len(data) + 16383) // 16384) + 128
     out = np.zeros(cap, np.uint8)
     n = ctypes.c_uint64()
     rc = L.emu_lz_deflate(ctypes.c_void_p(a.ctypes.data if len(data) else None), ctypes.c_uint64(len(data)),
                           ctypes.c_void_p(d.ctypes.data if len(dict_) else None), ctypes.c_uint32(len(dict_)),
                           ctypes.c_void_p(out.ctypes.data), ctypes.c_uint64(cap), ctypes.byref(n), ctypes.c_uint32(grid),
-                          ctypes.c_uint32(run_chunks | (chunk_units << 16)))
+                          ctypes.c_uint32(run_chunks | (chunk_units << 16) | ((small_chunk_kib // 16) << 24)))
     assert rc == 0
     return out[: n.value].tobytes()
 
@@ -162,3 +163,16 @@ def test_emulated_stored_exit_keeps_the_window_and_sees_copies():
     z = emu_deflate(mix, run_chunks=2, grid=1)
     assert zlib.decompress(z, -15) == mix
     assert len(z) < 65_536 + 5 * 2 + 0.45 * 50_000
+
+
+@pytest.mark.parametrize("kib", [16, 32])
+def test_emulated_small_chunks(kib):
+    """Small inputs are cut into 16 / 32 KiB chunks (one deflate block each, the 32 KiB dictionary unchanged)."""
+    data = realistic_text(70_001, 31) + helpers.rng_bytes(32, 20_000) + b"\0" * 9_000
+    z = emu_deflate(data, small_chunk_kib=kib, grid=2)
+    assert zlib.decompress(z, -15) == data
+    assert z == emu_deflate(data, small_chunk_kib=kib, grid=1)
+    assert len(z) <= 1.04 * len(emu_deflate(data))            # the price of more block headers
+    rnd = helpers.rng_bytes(33, 40_000)
+    z = emu_deflate(rnd, small_chunk_kib=kib)
+    assert zlib.decompress(z, -15) == rnd and len(z) <= len(rnd) + 5 * ((len(rnd) + kib * 1024 - 1) // (kib * 1024)) + 2

@@ -121,7 +121,7 @@ def test_level6_deflate_roundtrip(packer6, name):
     assert g[:10] == bytes.fromhex("1f8b08000000000000ff")
     assert struct.unpack("<II", g[-8:]) == (zlib.crc32(data), len(data) & 0xFFFFFFFF)
     assert gzip.decompress(g) == data
-    assert len(raw) <= len(data) + 10 * ((len(data) + 65535) // 65536) + 2       # never worse than stored chunks
+    assert len(raw) <= len(data) + 5 * ((len(data) + 16383) // 16384) + 2        # never worse than stored chunks
 
 
 # Judged equality (3): compressed size <= 1.03 x the oracle's zlib level-6 size. Measured on the B200
@@ -262,10 +262,16 @@ def test_level6_output_is_deterministic_and_equals_the_emulator(packer6):
     from test_emu_deflate import emu_deflate
     data = (synth.text_like(90_000, 31).numpy().tobytes() + b"\0" * 5000 + synth.binary_like(80_000, 32).numpy().tobytes()
             + synth.random_bytes(20_000, 33).numpy().tobytes())
-    a = packer6.deflate(data, level=6)
+    a = packer6.deflate(data, level=6)                      # 195 000 bytes: the host picks 32 KiB chunks
     assert a == packer6.deflate(data, level=6)
     assert zlib.decompress(a, -15) == data
-    assert a == emu_deflate(data, grid=2, run_chunks=1)
+    assert a == emu_deflate(data, grid=2, small_chunk_kib=32)
+    packer6.set_lz_geometry(chunk_units=1)                  # 64 KiB chunks
+    try:
+        b = packer6.deflate(data, level=6)
+    finally:
+        packer6.set_lz_geometry()
+    assert zlib.decompress(b, -15) == data and b == emu_deflate(data, grid=2, run_chunks=1)
     big = synth.binary_like(8_000_000, 34).numpy().tobytes()
     assert packer6.deflate(big, level=6) == packer6.deflate(big, level=6)
 
