@@ -42,6 +42,18 @@ def test_c1_quickstart_golden(packer):
     assert packer.pack(from_entries(es), tar_only=True) == t
 
 
+@pytest.mark.parametrize("case", ["name_101_nosplit", "uid_2097152"])
+def test_kernels_match_hand_derived_pax_bytes(packer, case):
+    """The PAX path of the header kernels against bytes derived by hand from the go1.11 source, independent of the oracle
+    (tests/golden/make_pax_hand.py)."""
+    import json
+    c = json.load(open(os.path.join(GOLD, "pax_hand_derived.json")))[case]
+    m = c["manifest"]
+    es = [helpers.F(m["name"], m["data"].encode(), mode=m["mode"], uid=m["uid"], gid=m["gid"], uname=m["uname"],
+                    gname=m["gname"], mtime=m["mtime"])]
+    assert packer.tar_stream(from_entries(es)) == bytes.fromhex(c["stream_hex"])
+
+
 def test_no_trailer_flag(packer):
     es = SUITE["mixed_tree"]
     assert packer.tar_stream(from_entries(es), flags=1) == oracle.tar_stream(es)[:-1024]

@@ -176,3 +176,20 @@ def test_piecewise_oracle_hash_and_streamed_gunzip_agree_with_the_whole_stream()
     assert (sha, n) == (hashlib.sha256(ref).hexdigest(), len(ref))
     two = gzip.compress(ref[:700_001], 1) + gzip.compress(ref[700_001:], 1)
     assert helpers.gunzip_sha256(two, piece=65_000) == (sha, n, 2)
+
+
+def _hand_derived():
+    import json
+    return json.load(open(os.path.join(GOLD, "pax_hand_derived.json")))
+
+
+@pytest.mark.parametrize("case", ["name_101_nosplit", "uid_2097152"])
+def test_oracle_matches_hand_derived_pax_bytes(case):
+    """tests/golden/make_pax_hand.py builds these streams field by field from the go1.11 archive/tar source without the
+    oracle (PaxHeaders.0 entry name, self-inclusive record length, name field cut without terminator, zeroed overflow
+    uid, NUL devmajor/devminor in the PAX block): a second derivation the oracle has to agree with."""
+    c = _hand_derived()[case]
+    m = c["manifest"]
+    es = [helpers.F(m["name"], m["data"].encode(), mode=m["mode"], uid=m["uid"], gid=m["gid"], uname=m["uname"],
+                    gname=m["gname"], mtime=m["mtime"])]
+    assert oracle.tar_stream(es) == bytes.fromhex(c["stream_hex"])
