@@ -124,8 +124,11 @@ enum { kMTicket = 0, kMStart, kMNTok, kMMode, kMOutLo, kMOutHi, kMHdrBits, kMChu
        kMFlat /* every 8 KiB of the chunk has a flat byte histogram */, kMProbe /* matches found in the first tile of
        every team */, kMStale /* the window has to be rebuilt before the next chunk */,
        kMScan = 32 /* CTA scan: 32 warp partials + carry; team scans: 20 words each */, kMTeamScan = kMScan,
-       kMTeamScanStride = 20, kMBulkBar = 176 /* kTeams mbarriers, 8 bytes each */ };
-static_assert(kMBulkBar % 2 == 0 && kMBulkBar + 2 * kTeams <= 192 && kMBulkBar >= 144, "mbarrier words in misc[]");
+       kMTeamScanStride = 20, kMSig = 144 /* kSigCount hand-off signals, 8 bytes each */,
+       kMBulkBar = 176 /* kTeams mbarriers, 8 bytes each */, kMTileCtr = 184 /* next tile of the chunk */,
+       kMTeamTile = 185 /* kTeams slots: the tile a team has just taken */ };
+static_assert(kMBulkBar % 2 == 0 && kMBulkBar + 2 * kTeams <= kMTileCtr && kMSig % 2 == 0 && kMSig + 2 * 16 <= kMBulkBar &&
+                  kMTeamTile + kTeams <= 192, "mbarrier words in misc[]");
 static_assert(kMStale < kMScan && kRun == 8 && kMTeamScan + kTeams * kMTeamScanStride <= 192, "misc[] slots");
 
 // Kernel parameter block
@@ -151,8 +154,7 @@ enum { kProfLoad = 0, kProfInsert, kProfSearch, kProfParse, kProfEmit, kProfHuff
        kProfWarpSearch = kProfCount, kProfWarpDeep, kProfSlots };
 
 // named barriers: 0 = the CTA
-enum { kBarTeam = 1 /* +team */, kBarInsert = kBarTeam + kTeams /* +producing team */,
-       kBarEmit = kBarInsert + kTeams /* +producing team */, kBarEnd = kBarEmit + kTeams };
+enum { kBarTeam = 1 /* +team */, kBarEnd = kBarTeam + kTeams };
 static_assert(kBarEnd <= 16, "an SM has 16 named barriers");
 
 DSG_D uint32_t ring_slot(int rp /* run-relative position, >= -kDict */) {
@@ -178,23 +180,51 @@ DSG_D void group_sync(const LzGroup &g) {
   }
 }
 
-// Producer/consumer hand-off between two teams on a named barrier: the producing team arrives (does not wait),
-// the consuming team waits; the barrier completes when the threads of both teams have done one or the other.
-DSG_D void handoff_arrive(int bar) {
+// Tile hand-offs between teams: "tile t is in the hash chains" and "tile t has emitted its tokens", each a one-shot
+// signal. A signal lives in a ring of kSigRing slots (slot t % kSigRing, use t / kSigRing) -- at most kTeams consecutive
+// tiles are in flight, so a slot is never armed again before its waiters have passed. On the GPU a slot is an mbarrier
+// with arrival count 1: ONE thread of the producing team arrives (release) after the team's own barrier, the
+// threads of the consuming team wait on the phase parity (try_wait sleeps in hardware instead of holding a named
+// barrier with 512 participants). Under the emulator a slot is a counter and the wait yields the fiber. The slots are
+// initialised once per CTA; tiles are numbered through all chunks the CTA compresses (seq_base), and EVERY tile that is
+// taken arrives exactly once on both of its signals, so slot and phase follow from the tile's number alone.
+constexpr int kSigRing = 8;
+enum { kSigIns = 0, kSigEmit = kSigRing, kSigCount = 2 * kSigRing };
+static_assert(kSigRing >= 2 * kTeams, "signal ring");
+
+#if defined(DSG_EMU)
+DSG_D void sig_init(uint32_t *sig, int i) { sig[2 * i] = 0; }
+DSG_D void sig_arrive(uint32_t *sig, int i) {
   __threadfence_block();
-#if defined(DSG_EMU)
-  emu::named_barrier_arrive(bar, 2 * kTeamThreads);
-#else
-  asm volatile("bar.arrive %0, %1;" ::"r"(bar), "r"(2 * kTeamThreads) : "memory");
-#endif
+  atomicAdd(&sig[2 * i], 1u);
 }
-DSG_D void handoff_wait(int bar) {
-#if defined(DSG_EMU)
-  emu::named_barrier_sync(bar, 2 * kTeamThreads);
-#else
-  asm volatile("bar.sync %0, %1;" ::"r"(bar), "r"(2 * kTeamThreads) : "memory");
-#endif
+DSG_D void sig_wait(uint32_t *sig, int i, uint32_t use) {
+  while (*reinterpret_cast<volatile uint32_t *>(&sig[2 * i]) < use + 1u) emu::yield();
 }
+#else
+DSG_D void sig_init(uint32_t *sig, int i) {
+  const uint32_t a = (uint32_t)__cvta_generic_to_shared(sig + 2 * i);
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(a), "r"(1) : "memory");
+}
+DSG_D void sig_arrive(uint32_t *sig, int i) {
+  const uint32_t a = (uint32_t)__cvta_generic_to_shared(sig + 2 * i);
+  asm volatile("mbarrier.arrive.release.cta.shared::cta.b64 _, [%0];" ::"r"(a) : "memory");
+}
+DSG_D void sig_wait(uint32_t *sig, int i, uint32_t use) {
+  const uint32_t a = (uint32_t)__cvta_generic_to_shared(sig + 2 * i);
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "SWAIT_%=:\n"
+      "mbarrier.try_wait.parity.acquire.cta.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra SDONE_%=;\n"
+      "bra SWAIT_%=;\n"
+      "SDONE_%=:\n"
+      "}\n" ::"r"(a),
+      "r"(use & 1u)
+      : "memory");
+}
+#endif
 
 // Shared-memory loads through 32-bit shared-window addresses. Inside the chain-walk loops the compiler otherwise
 // keeps the arrays as generic pointers and rebuilds the window base (S2UR/ULEA) in every iteration.
@@ -1219,7 +1249,6 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   // the team's private arrays
   const uint32_t team = warp / kTeamWarps;
-  const uint32_t prev_team = (team + kTeams - 1) % kTeams;  // owns the tile before each of ours
   const LzGroup g_team{(int)(tid - team * kTeamThreads), kTeamThreads, kBarTeam + (int)team};
   uint8_t *t_mlen = s_mlen + team * kTile;
   uint16_t *t_mdist = s_mdist + team * kTile;
@@ -1235,12 +1264,19 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
   const uint32_t t_mbar = (uint32_t)__cvta_generic_to_shared(s_misc + kMBulkBar + 2 * team);
   if (tid == 0) {
     for (int i = 0; i < kTeams; i++) mbar_init((uint32_t)__cvta_generic_to_shared(s_misc + kMBulkBar + 2 * i), 1);
+    for (int i = 0; i < kSigCount; i++) sig_init(s_misc + kMSig, i);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
 #else
   const uint32_t t_mbar = 0;
 #endif
+  uint32_t *s_sig = s_misc + kMSig;
+#if defined(DSG_EMU)
+  if (tid < (uint32_t)kSigCount) sig_init(s_sig, (int)tid);
+  __syncthreads();
+#endif
+  uint32_t seq_base = 0;  // number of the chunk's first tile in the CTA's running tile count (uniform)
 
   long long t_last = 0;
 #define LZ_PROF(k)                                                    \
@@ -1303,6 +1339,7 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
       s_misc[kMStart] = 0;
       s_misc[kMNTok] = 0;
       s_misc[kMProbe] = 0;
+      s_misc[kMTileCtr] = (uint32_t)kTeams;  // every team's first tile is its own number, the later ones are taken
     }
     chunk_flatness(P.in, P.len, cs, chunk_len, reinterpret_cast<uint32_t *>(s_work), &s_misc[kMFlat]);  // barriers inside
     __syncthreads();
@@ -1319,7 +1356,12 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
     // every team has a first tile, so the CTA-wide barrier behind it is reached by all threads
     const bool flat_candidate = s_misc[kMFlat] != 0u && ntiles >= kTeams;
     bool stored_exit = false;
-    for (int t = (int)team; t < ntiles; t += kTeams) {
+    // Tiles are TAKEN, not dealt: a team that has emitted its tile takes the next free one (shared counter), so a team
+    // with a cheap tile (random or zero page) does not sit out the turn of a team with an expensive one (token-like
+    // text: three times the deep-search work). Hashing and emission stay in tile order through the signals; at most
+    // kTeams consecutive tiles are in flight (a team cannot emit, hence not take a tile, before its predecessor has).
+    int t = (int)team;
+    while (t < ntiles) {
       const int tile_rp = crp + t * kTile;
       const int tile_len = chunk_len - t * kTile < kTile ? chunk_len - t * kTile : kTile;
       const bool has_next = t + 1 < ntiles;
@@ -1336,7 +1378,8 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
         load_ring(s_data, P, rs, tile_rp + kLook, tile_rp + kTile + kLook, g_team);
       }
       LZ_PROF(kProfLoad);
-      if (t > 0) handoff_wait(kBarInsert + (int)prev_team);  // tile t-1 is in the chains
+      const uint32_t seq = seq_base + (uint32_t)t;  // t > 0: seq - 1 is the previous tile of this chunk
+      if (t > 0) sig_wait(s_sig, kSigIns + (int)((seq - 1) & (kSigRing - 1)), (seq - 1) / kSigRing);  // tile t-1 is in the chains
       LZ_PROF(kProfWaitA);
       if (bulk) {
 #if !defined(DSG_EMU)
@@ -1349,7 +1392,7 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
       LZ_PROF(kProfLoad);
       insert_positions(s_data, s_prev, s_head, tile_rp, tile_rp + tile_len, lo_rp, g_team, t_scan,
                        &s_misc[kMRunStart]);  // ends with a barrier
-      if (has_next) handoff_arrive(kBarInsert + (int)team);
+      if (g_team.tid == 0) sig_arrive(s_sig, kSigIns + (int)(seq & (kSigRing - 1)));  // (behind the team barrier)
       LZ_PROF(kProfInsert);
       if (g_team.tid == 0) *t_ctr = 0;
       for (uint32_t i = (uint32_t)g_team.tid; i < (uint32_t)kTile / 32; i += kTeamThreads) t_deep[i] = 0;
@@ -1371,8 +1414,8 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
         if (lane == 0 && found) atomicAdd(&s_misc[kMProbe], found);
         __syncthreads();
         if (s_misc[kMProbe] <= (uint32_t)kFlatMaxMatches) {
-          // The chunk is stored. Team 3's hand-off for tile 4 is the one arrival nobody has consumed yet.
-          if (team == 0 && ntiles > kTeams) handoff_wait(kBarInsert + kTeams - 1);
+          // The chunk is stored. Every tile that was taken completes both of its signals.
+          if (g_team.tid == 0) sig_arrive(s_sig, kSigEmit + (int)(seq & (kSigRing - 1)));
           stored_exit = true;
           break;
         }
@@ -1395,7 +1438,7 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
         LZ_PROF(kProfRefDeep);
       }
       // -- stage C: final parse and token emission, in tile order
-      if (t > 0) handoff_wait(kBarEmit + (int)prev_team);  // tile t-1 has emitted: kMStart and kMNTok are ours
+      if (t > 0) sig_wait(s_sig, kSigEmit + (int)((seq - 1) & (kSigRing - 1)), (seq - 1) / kSigRing);  // tile t-1 has emitted: kMStart and kMNTok are ours
       LZ_PROF(kProfWaitB);
       const int nxt = parse_tile_wide(t_mlen, t_bitmap, (int)s_misc[kMStart], tile_len, g_team);
       LZ_PROF(kProfParse);
@@ -1430,13 +1473,17 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
         if (g_team.tid == 0) {
           s_misc[kMNTok] = base + total;
           s_misc[kMStart] = (uint32_t)nxt;
+          sig_arrive(s_sig, kSigEmit + (int)(seq & (kSigRing - 1)));  // release: the two words above are visible
+          s_misc[kMTeamTile + team] = atomicAdd(&s_misc[kMTileCtr], 1u);    // the team's next tile
         }
-        if (has_next) handoff_arrive(kBarEmit + (int)team);
+        group_sync(g_team);
+        t = (int)s_misc[kMTeamTile + team];
       }
       LZ_PROF(kProfEmit);
     }
     __syncthreads();
     LZ_PROF(kProfJoin);
+    seq_base += stored_exit ? (uint32_t)kTeams : (uint32_t)ntiles;  // the tiles that were taken (and have signalled)
     if (stored_exit) {  // uniform: decided from shared memory behind a CTA-wide barrier
       if (tid == 0) {
         const uint32_t n_stored_blocks = ((uint32_t)chunk_len + kStoredMax - 1) / kStoredMax;
