@@ -11,7 +11,7 @@ LIB_PATH = os.path.join(HERE, "libdsgpack.so")
 
 DSG_OK = 0
 DSG_E_ARG, DSG_E_CUDA, DSG_E_HEADER, DSG_E_TYPEFLAG = -1, -2, -3, -4
-DSG_E_CAPACITY, DSG_E_UNCLEAN_NAME, DSG_E_NOMEM, DSG_E_RANGE = -5, -6, -7, -8
+DSG_E_CAPACITY, DSG_E_UNCLEAN_NAME, DSG_E_NOMEM, DSG_E_RANGE, DSG_E_CORRUPT = -5, -6, -7, -8, -9
 DSG_LEVEL_STORED, DSG_LEVEL_DEFAULT = 0, 6
 DSG_F_NO_TRAILER = 1
 DSG_LZ_TAIL_SET, DSG_LZ_PROFILE = 1, 2
@@ -26,7 +26,7 @@ SYMBOLS = [
     "dsg_dev_download", "dsg_crc32_noalloc", "dsg_file_crc32", "dsg_dev_file_crc32", "dsg_directory_hash", "dsg_docker_context_tar", "dsg_walk", "dsg_written_count", "dsg_written_get",
     "dsg_written_entries", "dsg_written_free", "dsg_write_tar",
     "dsg_multi_create", "dsg_multi_destroy", "dsg_multi_last_error", "dsg_multi_shards", "dsg_multi_get_stats",
-    "dsg_multi_pack_fd", "dsg_multi_pack",
+    "dsg_multi_pack_fd", "dsg_multi_pack", "dsg_gunzip", "dsg_dev_gunzip",
 ]
 DSG_MULTI_ONE_MEMBER = 1
 
@@ -112,6 +112,8 @@ def load(build_if_missing: bool = True):
     lib.dsg_crc32_noalloc.argtypes = [vp, sz, POINTER(c_uint32), c_char_p, sz]
     lib.dsg_file_crc32.argtypes = [vp, vp, sz, vp, sz, vp]
     lib.dsg_dev_file_crc32.argtypes = [vp, vp, sz, vp, sz, vp]
+    lib.dsg_gunzip.argtypes = [vp, vp, sz, vp, sz, POINTER(sz)]
+    lib.dsg_dev_gunzip.argtypes = [vp, vp, sz, vp, sz, POINTER(sz)]
     lib.dsg_crc32_combine.argtypes = [c_uint32, c_uint32, c_uint64]
     lib.dsg_crc32_combine.restype = c_uint32
     lib.dsg_multi_create.argtypes = [POINTER(c_int), c_int, POINTER(DsgOpts), POINTER(vp)]

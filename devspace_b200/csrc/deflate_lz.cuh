@@ -1430,6 +1430,8 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
         LZ_PROF(kProfRefParse);
         const uint32_t nwork = refine_build_list(t_mlen, t_mdist, t_bitmap, t_deep, t_work, t_scan, tile_len, g_team);
         LZ_PROF(kProfRefList);
+        if (nwork == 0) break;  // nothing to look at more deeply (random, zero and record pages): a further round would
+                                // parse the same lengths again and find the same empty list (uniform: nwork is a scan total)
         const long long t_wd = P.prof ? clock64() : 0;
         refine_search(s_data, s_prev, t_mlen, t_mdist, t_work, nwork, tile_rp, tile_len, crp + chunk_len, lo_rp, t_ctr);
         if (P.prof && team == 0 && lane == 0)

@@ -20,6 +20,7 @@
 #include "crc32.cuh"
 #include "deflate_lz.cuh"
 #include "file_crc.cuh"
+#include "inflate.cuh"
 #include "deflate_stored.cuh"
 #include "tar_kernels.cuh"
 
@@ -85,6 +86,8 @@ struct dsg_ctx {
   DevBuf lz_scratch, chunk_sizes, chunk_slots, chunk_offs, lz_prof;
   // pipelined path: two slots each for the arena slice, the tar segment and the compressed segment
   DevBuf slot_arena[2], slot_tar[2], slot_out[2], seg_ranges;
+  // gunzip (inflate.cuh)
+  DevBuf gz_counts, gz_cand, gz_rec, gz_units, gz_members, gz_sym, gz_misc, gz_in, gz_out;
   Timer tim[kTimCount];
   uint64_t *h_scalars = nullptr;  // pinned mirror of `scalars`
   uint8_t *h_stage[2] = {nullptr, nullptr};  // pinned staging of the file-descriptor sink (dsg_pack_fd)
@@ -479,6 +482,7 @@ const char *dsg_strerror(int status) {
     case DSG_E_UNCLEAN_NAME: return "PAX entry name is not path.Clean()ed";
     case DSG_E_NOMEM: return "out of device or pinned memory";
     case DSG_E_RANGE: return "payload range outside the arena";
+    case DSG_E_CORRUPT: return "gzip stream fails its structure or CRC32 check";
     default: return "unknown status";
   }
 }
@@ -568,7 +572,8 @@ void dsg_ctx_destroy(dsg_ctx *ctx) {
   for (DevBuf *b : {&ctx->crc_tab, &ctx->crc_shift, &ctx->ent_blocks, &ctx->cta_sums, &ctx->ent_off, &ctx->scalars,
                     &ctx->d_entries, &ctx->d_strtab, &ctx->d_arena, &ctx->d_tar, &ctx->d_out, &ctx->crc_raw,
                     &ctx->fc_files, &ctx->fc_units, &ctx->fc_first, &ctx->fc_totals, &ctx->fc_raw, &ctx->fc_crcs,
-                    &ctx->lz_scratch, &ctx->chunk_sizes, &ctx->chunk_slots, &ctx->chunk_offs, &ctx->lz_prof, &ctx->seg_ranges, &ctx->slot_arena[0],
+                    &ctx->gz_counts, &ctx->gz_cand, &ctx->gz_rec, &ctx->gz_units, &ctx->gz_members, &ctx->gz_sym,
+                    &ctx->gz_misc, &ctx->gz_in, &ctx->gz_out, &ctx->lz_scratch, &ctx->chunk_sizes, &ctx->chunk_slots, &ctx->chunk_offs, &ctx->lz_prof, &ctx->seg_ranges, &ctx->slot_arena[0],
                     &ctx->slot_arena[1], &ctx->slot_tar[0], &ctx->slot_tar[1], &ctx->slot_out[0], &ctx->slot_out[1]})
     b->release();
   for (auto &t : ctx->tim) {
@@ -1436,3 +1441,153 @@ int dsg_get_stats(const dsg_ctx *ctx, dsg_stats *out) {
 }
 
 }  // extern "C"
+
+// ---- gunzip of this library's own streams (downstream direction, tar.go:16-33) ----------------------------------------
+
+namespace {
+int gunzip_device(dsg_ctx *ctx, const uint8_t *d_in, uint64_t n, uint8_t *d_out, uint64_t out_cap, uint64_t *out_len) {
+  cudaStream_t st = ctx->stream;
+  *out_len = 0;
+  if (n < 20) return fail(ctx, DSG_E_ARG, "not a gzip stream of this library: %llu bytes", (unsigned long long)n);
+  if (n > 0xffffffffull * (uint64_t)kGzScanCta / 2) return fail(ctx, DSG_E_ARG, "input too large for one call");
+  // 1. candidate unit starts
+  const uint32_t ncta = (uint32_t)((n + kGzScanCta - 1) / kGzScanCta);
+  CU(ctx->gz_counts.ensure(sizeof(uint32_t) * 2 * (size_t)ncta + 64));
+  uint32_t *d_counts = ctx->gz_counts.as<uint32_t>(), *d_offs = d_counts + ncta;
+  gz_scan_count<<<ncta, kGzScanThreads, 0, st>>>(d_in, n, d_counts);
+  LAUNCH_CHECK();
+  std::vector<uint32_t> counts(ncta);
+  CU(cudaMemcpyAsync(counts.data(), d_counts, sizeof(uint32_t) * ncta, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  uint64_t total = 0;
+  for (uint32_t i = 0; i < ncta; i++) {
+    const uint32_t c = counts[i];
+    counts[i] = (uint32_t)total;
+    total += c;
+  }
+  if (total == 0 || total > 0x7fffffffull) return fail(ctx, DSG_E_ARG, "not a gzip stream of this library (no unit starts found)");
+  CU(cudaMemcpyAsync(d_offs, counts.data(), sizeof(uint32_t) * ncta, cudaMemcpyHostToDevice, st));
+  CU(ctx->gz_cand.ensure(sizeof(uint64_t) * (size_t)total + 64));
+  uint64_t *d_cand = ctx->gz_cand.as<uint64_t>();
+  gz_scan_write<<<ncta, kGzScanThreads, 0, st>>>(d_in, n, d_offs, d_cand);
+  LAUNCH_CHECK();
+  std::vector<uint64_t> cand((size_t)total);
+  CU(cudaMemcpyAsync(cand.data(), d_cand, sizeof(uint64_t) * total, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  std::sort(cand.begin(), cand.end());
+  cand.erase(std::unique(cand.begin(), cand.end()), cand.end());
+  const uint32_t ncand = (uint32_t)cand.size();
+  CU(cudaMemcpyAsync(d_cand, cand.data(), sizeof(uint64_t) * ncand, cudaMemcpyHostToDevice, st));
+  // 2. dry decode of every candidate, 3. the chain
+  CU(ctx->gz_rec.ensure(sizeof(GzRec) * (size_t)ncand + 64));
+  GzRec *d_rec = ctx->gz_rec.as<GzRec>();
+  gz_measure_kernel<<<(ncand + kGzWarpsPerCta - 1) / kGzWarpsPerCta, 32 * kGzWarpsPerCta, 0, st>>>(d_in, n, d_cand, ncand, d_rec);
+  LAUNCH_CHECK();
+  const uint32_t max_units = ncand + 16, max_members = 65536;
+  CU(ctx->gz_units.ensure(sizeof(GzUnit) * (size_t)max_units));
+  CU(ctx->gz_members.ensure(sizeof(GzMember) * (size_t)max_members));
+  CU(ctx->gz_misc.ensure(sizeof(GzSummary) + 64));
+  GzUnit *d_units = ctx->gz_units.as<GzUnit>();
+  GzMember *d_members = ctx->gz_members.as<GzMember>();
+  GzSummary *d_sum = ctx->gz_misc.as<GzSummary>();
+  uint32_t *d_err = reinterpret_cast<uint32_t *>(d_sum + 1);
+  CU(cudaMemsetAsync(d_err, 0, sizeof(uint32_t), st));
+  gz_chain_kernel<<<1, 32, 0, st>>>(d_in, n, d_cand, d_rec, ncand, d_units, max_units, d_members, max_members, d_sum);
+  LAUNCH_CHECK();
+  GzSummary S;
+  CU(cudaMemcpyAsync(&S, d_sum, sizeof S, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  if (S.status == DSG_E_CAPACITY) return fail(ctx, DSG_E_ARG, "gzip stream has more members than one call takes");
+  if (S.status != DSG_OK)
+    return fail(ctx, DSG_E_ARG, "not a gzip stream written by this library (structure breaks at byte %llu): only "
+                "streams of dsg_pack* can be inflated in parallel", (unsigned long long)S.bad_offset);
+  *out_len = S.total_out;
+  ctx->stats.tar_bytes = S.total_out;
+  ctx->stats.segments = S.nmembers;
+  if (S.total_out > out_cap)
+    return fail(ctx, DSG_E_CAPACITY, "output needs %llu bytes, capacity %llu", (unsigned long long)S.total_out,
+                (unsigned long long)out_cap);
+  if (S.nunits == 0) return DSG_OK;
+  // 4. decode into 16-bit symbols, stored blocks straight to the output, then resolve the window references
+  CU(ctx->gz_sym.ensure(sizeof(uint16_t) * (size_t)S.total_out + 64));
+  uint16_t *d_sym = ctx->gz_sym.as<uint16_t>();
+  tic(ctx, kTimDeflate);
+  gz_decode_kernel<<<(S.nunits + kGzWarpsPerCta - 1) / kGzWarpsPerCta, 32 * kGzWarpsPerCta, 0, st>>>(d_in, n, d_units, S.nunits, d_sym, d_err);
+  LAUNCH_CHECK();
+  gz_stored_copy_kernel<<<S.nunits, 256, 0, st>>>(d_in, d_units, S.nunits, d_out);
+  LAUNCH_CHECK();
+  CU(ctx->gz_counts.ensure(sizeof(uint32_t) * (size_t)S.nunits + 64));  // (the scan counters are done with)
+  uint32_t *d_fix = ctx->gz_counts.as<uint32_t>();
+  gz_tails_plain<<<S.nunits, 256, 0, st>>>(d_units, S.nunits, d_sym, d_out, d_fix);
+  LAUNCH_CHECK();
+  gz_tails_kernel<<<1, 1024, 0, st>>>(d_units, S.nunits, d_sym, d_out, d_fix);
+  LAUNCH_CHECK();
+  gz_bodies_kernel<<<S.nunits, 256, 0, st>>>(d_units, S.nunits, d_sym, d_out);
+  LAUNCH_CHECK();
+  toc(ctx, kTimDeflate);
+  uint32_t h_err = 0;
+  CU(cudaMemcpyAsync(&h_err, d_err, sizeof h_err, cudaMemcpyDeviceToHost, st));
+  std::vector<GzMember> members(S.nmembers);
+  CU(cudaMemcpyAsync(members.data(), d_members, sizeof(GzMember) * S.nmembers, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  if (h_err) return fail(ctx, DSG_E_CORRUPT, "unit %u decodes differently in the second pass", h_err - 1);
+  // 5. every member's CRC32 (ISIZE was checked by the chain walk)
+  uint32_t *state = reinterpret_cast<uint32_t *>(ctx->scalars.as<uint64_t>() + kSCrc);
+  tic(ctx, kTimCrc);
+  for (uint32_t m = 0; m < S.nmembers; m++) {
+    int rc = crc_reset(ctx);
+    if (rc) return rc;
+    if ((rc = crc_update(ctx, d_out + members[m].out_off, members[m].out_len))) return rc;
+    uint32_t got[2] = {0, 0};
+    CU(cudaMemcpyAsync(got, state, sizeof got, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (got[0] != members[m].crc)
+      return fail(ctx, DSG_E_CORRUPT, "member %u: CRC32 %08x, trailer says %08x", m, got[0], members[m].crc);
+    ctx->stats.crc32 = got[0];
+  }
+  toc(ctx, kTimCrc);
+  return DSG_OK;
+}
+}  // namespace
+
+extern "C" int dsg_dev_gunzip(dsg_ctx *ctx, const uint8_t *d_in, size_t in_len, uint8_t *d_out, size_t out_cap,
+                              size_t *out_len) {
+  if (!ctx || !d_in || !out_len || (out_cap && !d_out)) return DSG_E_ARG;
+  std::lock_guard<std::mutex> g(ctx->mu);
+  int rc = begin_call(ctx);
+  if (rc) return rc;
+  tic(ctx, kTimTotal);
+  uint64_t produced = 0;
+  rc = gunzip_device(ctx, d_in, in_len, d_out, out_cap, &produced);
+  *out_len = (size_t)produced;
+  if (rc) return rc;
+  toc(ctx, kTimTotal);
+  CU(cudaStreamSynchronize(ctx->stream));
+  ctx->stats.payload_bytes = in_len;
+  finish_stats(ctx, produced);
+  return DSG_OK;
+}
+
+extern "C" int dsg_gunzip(dsg_ctx *ctx, const uint8_t *in, size_t in_len, uint8_t *out, size_t out_cap, size_t *out_len) {
+  if (!ctx || !in || !out_len || (out_cap && !out)) return DSG_E_ARG;
+  std::lock_guard<std::mutex> g(ctx->mu);
+  int rc = begin_call(ctx);
+  if (rc) return rc;
+  CU(ctx->gz_in.ensure(in_len + 64));
+  // ISIZE of the last member bounds nothing (mod 2^32, several members): the output buffer is sized from out_cap
+  CU(ctx->gz_out.ensure(out_cap + 64));
+  tic(ctx, kTimTotal);
+  CU(cudaMemcpyAsync(ctx->gz_in.p, in, in_len, cudaMemcpyHostToDevice, ctx->stream));
+  uint64_t produced = 0;
+  rc = gunzip_device(ctx, ctx->gz_in.as<uint8_t>(), in_len, ctx->gz_out.as<uint8_t>(), out_cap, &produced);
+  *out_len = (size_t)produced;
+  if (rc) return rc;
+  if (produced) CU(cudaMemcpyAsync(out, ctx->gz_out.p, produced, cudaMemcpyDeviceToHost, ctx->stream));
+  toc(ctx, kTimTotal);
+  CU(cudaStreamSynchronize(ctx->stream));
+  ctx->stats.payload_bytes = in_len;
+  ctx->stats.h2d_bytes = in_len;
+  ctx->stats.d2h_bytes = produced;
+  finish_stats(ctx, produced);
+  return DSG_OK;
+}

@@ -249,6 +249,21 @@ class Packer:
         finally:
             d.free()
 
+    def gunzip(self, blob, out_cap: Optional[int] = None) -> bytes:
+        """dsg_gunzip: chunk-parallel inflate of a (multi-member) gzip stream this library wrote; the tar stream back.
+        out_cap defaults to the sum the member trailers promise (read on the host: ISIZE of every member is only
+        known after the walk, so the default asks the library once with no buffer)."""
+        a = np.frombuffer(bytes(blob), np.uint8) if not isinstance(blob, np.ndarray) else blob
+        n = c_size_t()
+        if out_cap is None:
+            rc = self._lib.dsg_gunzip(self._ctx, _ptr(a), a.size, c_void_p(0), 0, byref(n))
+            if rc not in (0, _lib.DSG_E_CAPACITY):
+                self._check(rc)
+            out_cap = n.value
+        out = np.empty(max(out_cap, 1), np.uint8)
+        self._check(self._lib.dsg_gunzip(self._ctx, _ptr(a), a.size, _ptr(out), out_cap, byref(n)))
+        return out[: n.value].tobytes()
+
     def deflate(self, data, level: Optional[int] = None, gzip: bool = False) -> bytes:
         a = np.frombuffer(bytes(data), np.uint8) if not isinstance(data, np.ndarray) else data
         d_in = DeviceBuffer(self, a.size + 16).upload(a)

@@ -39,7 +39,8 @@ typedef enum dsg_status {
   DSG_E_CAPACITY = -5,   /* caller's output buffer too small; required size in *out_len             */
   DSG_E_UNCLEAN_NAME = -6, /* a PAX entry's name is not path.Clean()ed (tar.go names always are)    */
   DSG_E_NOMEM = -7,      /* device / pinned allocation failed                                       */
-  DSG_E_RANGE = -8       /* payload range outside the arena                                         */
+  DSG_E_RANGE = -8,      /* payload range outside the arena                                         */
+  DSG_E_CORRUPT = -9     /* dsg_gunzip: the stream fails its structure or CRC32 check                */
 } dsg_status;
 
 /*
@@ -312,6 +313,21 @@ int dsg_dev_gzip(dsg_ctx *ctx, const uint8_t *d_in, size_t len, int level, uint8
  * capture). All calls on a device share the array: do not let two calls overlap on the GPU. Runs on the default
  * stream and returns once *crc (host memory) holds the result. err/err_len: optional buffer for error text. */
 int dsg_crc32_noalloc(const uint8_t *d_buf, size_t len, uint32_t *crc, char *err, size_t err_len);
+
+/* ---- downstream direction ------------------------------------------------------------------ *
+ * Replaces the decompression half of untarAll, tar.go:16-33 (gzip.NewReader(reader) in front of tar.NewReader), for
+ * archives that THIS LIBRARY packed -- the case SURVEY.md names as the one worth accelerating: both ends run the
+ * packer (a GPU pod packs the downstream archive instead of `tar -czf`, downstream.go:394). Such a stream inflates
+ * chunk-parallel: every chunk starts on a byte boundary behind a sync marker or a stored block, the unit starts are
+ * found without decoding, every unit is decoded on its own thread, and the references a chunk makes into the 32 KiB
+ * before it are resolved afterwards (devspace_b200/csrc/inflate.cuh). Multi-member streams (dsg_multi_*, shard
+ * members back to back) are taken as they are. Every member's ISIZE and CRC32 are checked. `out` receives the tar
+ * stream; tar parsing and the file writes of untarNext (tar.go:36-144) stay on the host.
+ * A gzip stream of any other writer (GNU gzip, Go) is one chain of bits and is refused with DSG_E_ARG -- there is no
+ * serial fallback on the GPU and none on the CPU; the caller keeps gzip.NewReader for those. DSG_E_CAPACITY with
+ * *out_len = the size needed; DSG_E_CORRUPT when a member fails its CRC32. */
+int dsg_gunzip(dsg_ctx *ctx, const uint8_t *in, size_t in_len, uint8_t *out, size_t out_cap, size_t *out_len);
+int dsg_dev_gunzip(dsg_ctx *ctx, const uint8_t *d_in, size_t in_len, uint8_t *d_out, size_t out_cap, size_t *out_len);
 
 /* Plain device memory helpers so that ctypes / cgo callers need no CUDA binding of their own. */
 void *dsg_dev_alloc(dsg_ctx *ctx, size_t bytes);

@@ -6,11 +6,13 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <algorithm>
 #include <vector>
 
 #include "crc32.cuh"
 #include "deflate_lz.cuh"
 #include "file_crc.cuh"
+#include "inflate.cuh"
 #include "tar_kernels.cuh"
 
 dim3 threadIdx, blockIdx, blockDim, gridDim;
@@ -174,6 +176,57 @@ int emu_file_crc32(const uint8_t *entries, uint32_t n, uint32_t stride, uint32_t
 int emu_huff_lengths(const uint32_t *freq, int n, int max_bits, uint8_t *lens) {
   static HuffScratch S;
   return huff_build_lengths(freq, n, max_bits, lens, S);
+}
+
+
+// Mirrors gunzip_device in dsgpack.cu: candidate scan -> dry decode -> chain -> decode -> stored copy -> tails ->
+// bodies. Returns 0, DSG_E_ARG (not a stream of this library), DSG_E_CAPACITY or DSG_E_CORRUPT (second pass differs);
+// crcs_ok = every member's CRC32 matches (checked here with the serial table-free recurrence, test infrastructure).
+int emu_gunzip(const uint8_t *in, uint64_t n, uint8_t *out, uint64_t cap, uint64_t *out_len, uint32_t *nunits_out,
+               uint32_t *nmembers_out, uint32_t *ncand_out) {
+  *out_len = 0;
+  if (n < 20) return DSG_E_ARG;
+  const uint32_t ncta = (uint32_t)((n + kGzScanCta - 1) / kGzScanCta);
+  std::vector<uint32_t> counts(ncta, 0), offs(ncta, 0);
+  emu::launch(dim3(ncta), dim3(kGzScanThreads), 0, [&] { gz_scan_count(in, n, counts.data()); });
+  uint64_t total = 0;
+  for (uint32_t i = 0; i < ncta; i++) {
+    offs[i] = (uint32_t)total;
+    total += counts[i];
+  }
+  if (total == 0) return DSG_E_ARG;
+  std::vector<uint64_t> cand(total);
+  emu::launch(dim3(ncta), dim3(kGzScanThreads), 0, [&] { gz_scan_write(in, n, offs.data(), cand.data()); });
+  std::sort(cand.begin(), cand.end());
+  cand.erase(std::unique(cand.begin(), cand.end()), cand.end());
+  const uint32_t ncand = (uint32_t)cand.size();
+  if (ncand_out) *ncand_out = ncand;
+  std::vector<GzRec> rec(ncand);
+  emu::launch(dim3((ncand + kGzWarpsPerCta - 1) / kGzWarpsPerCta), dim3(32 * kGzWarpsPerCta), 0, [&] { gz_measure_kernel(in, n, cand.data(), ncand, rec.data()); });
+  std::vector<GzUnit> units(ncand + 16);
+  std::vector<GzMember> members(4096);
+  GzSummary S;
+  emu::launch(dim3(1), dim3(32), 0, [&] {
+    gz_chain_kernel(in, n, cand.data(), rec.data(), ncand, units.data(), (uint32_t)units.size(), members.data(),
+                    (uint32_t)members.size(), &S);
+  });
+  if (S.status != DSG_OK) return DSG_E_ARG;
+  *out_len = S.total_out;
+  if (nunits_out) *nunits_out = S.nunits;
+  if (nmembers_out) *nmembers_out = S.nmembers;
+  if (S.total_out > cap) return DSG_E_CAPACITY;
+  if (S.nunits == 0) return 0;
+  std::vector<uint16_t> sym(S.total_out + 8, 0xEEEE);
+  uint32_t err = 0;
+  emu::launch(dim3((S.nunits + kGzWarpsPerCta - 1) / kGzWarpsPerCta), dim3(32 * kGzWarpsPerCta), 0,
+              [&] { gz_decode_kernel(in, n, units.data(), S.nunits, sym.data(), &err); });
+  if (err) return DSG_E_CORRUPT;
+  emu::launch(dim3(S.nunits), dim3(256), 0, [&] { gz_stored_copy_kernel(in, units.data(), S.nunits, out); });
+  std::vector<uint32_t> fix(S.nunits, 7);
+  emu::launch(dim3(S.nunits), dim3(256), 0, [&] { gz_tails_plain(units.data(), S.nunits, sym.data(), out, fix.data()); });
+  emu::launch(dim3(1), dim3(1024), 0, [&] { gz_tails_kernel(units.data(), S.nunits, sym.data(), out, fix.data()); });
+  emu::launch(dim3(S.nunits), dim3(256), 0, [&] { gz_bodies_kernel(units.data(), S.nunits, sym.data(), out); });
+  return 0;
 }
 
 }  // extern "C"
