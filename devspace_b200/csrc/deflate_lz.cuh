@@ -9,21 +9,27 @@
 // concatenate by byte copy. The previous 32 KiB of INPUT serve as the chunk's dictionary (same member, so
 // back-references into it are legal), which keeps the size within ~1 % of a serial level-6 stream.
 //
-// One persistent kernel (grid = #SMs, 512 threads, ~200 KB shared memory, 1 CTA/SM):
-//   per chunk   ticket = atomicAdd(counter)                        (chunks start in index order)
-//   per 8 KiB tile of the chunk:
-//     load      tile bytes -> shared-memory ring (dictionary 32 KiB + tile 8 KiB + look-ahead)
-//     insert    hash of 4 bytes -> head[8192] via atomicExch, prev[] links as 16-bit ring slots
-//               (shared-memory atomicExch measured at LDS rate on B200: profiles/r01_microbench.jsonl)
-//     search    one thread per run of 16 consecutive positions walks the hash chain (depth <= 48, nice 128,
-//               good 8); a position inherits (len-1, dist) from its predecessor, so positions inside a long
-//               match cost one probe instead of a full compare
-//     parse     stateless lazy rule next(p) = p + (len[p] >= 4 && len[p+1] <= len[p] ? len[p] : 1); the orbit of
-//               the chunk start under next() is found by 32 lanes parsing 256-position sub-ranges
-//               speculatively and a serial fix-up that stops at the first already-marked position
-//     emit      token starts -> block-wide rank (scan) -> 32-bit tokens to a per-CTA global scratch (L2
-//               resident) + shared-memory histograms
-//   per chunk   Huffman code lengths (two-queue merge, zlib-style overflow repair), code-length RLE, exact
+// One persistent kernel (grid = #SMs, 1024 threads, 64 registers, 212 KB shared memory, 1 CTA/SM):
+//   per run     ticket = atomicAdd(counter): a run of up to 8 consecutive chunks with ONE sliding window (chunks of
+//               16 / 32 KiB for small inputs, 64 / 128 / 256 KiB for large ones; the last chunks of a launch one by one)
+//   per chunk   a sampled byte histogram of every 8 KiB: flat chunks (random bytes) whose first tiles find no match
+//               leave through a stored exit; the window is rebuilt from the stream behind them
+//   per 2 KiB tile, by one of FOUR teams of 8 warps (a team takes the next free tile when it has emitted its own;
+//   hashing and emission stay in tile order through one-shot mbarrier signals; at most four consecutive tiles in flight):
+//     load      cp.async.bulk (the TMA engine's 1-D copy) + mbarrier into the 40 KiB ring (32 KiB window + one tile
+//               per team + look-ahead), issued before the wait for the previous tile's hashing
+//     insert    13-bit hash of 4 bytes; EXACT-order chains: lock-free sorted insertion (32-bit CAS on a lap-stamped
+//               head word, 16-bit CAS on a prev[] link), rounds of 256 positions; run interiors are not inserted
+//     search    shallow pass over EVERY position (depth 2, nice 128, good 8): per-lane state machine over runs of 8
+//               positions handed out through a shared counter; a position inherits (len-1, dist) from its predecessor
+//     refine    up to two rounds: stateless lazy parse from the tile start -> work list of the token starts and lazy
+//               successors whose shallow walk hit the depth limit -> deep search of only those (depth 160 / 40, links
+//               chased four ahead); a round with an empty list ends the refinement
+//     parse     stateless lazy rule next(p) = p + (len[p] >= 4 && len[p+1] <= len[p] ? len[p] : 1) from the carried
+//               position: one bitmap word per lane, exits travel by shuffle until nothing changes
+//     emit      token starts -> team-wide rank (scan) -> 32-bit tokens to a per-CTA global scratch (L2 resident) +
+//               shared-memory histograms
+//   per chunk   Huffman code lengths (rank sort, two-queue merge, zlib-style overflow repair), code-length RLE, exact
 //               sizes of the three encodings -> chunk size known BEFORE any bit is written
 //               bit packing: per-token bit lengths -> block scan -> atomicOr into a shared-memory window ->
 //               128-bit stores into the chunk's slot of a scratch buffer (stored chunks write nothing)
@@ -44,7 +50,7 @@ namespace dsg {
 constexpr int kLzThreads = 1024;
 constexpr int kLzWarps = kLzThreads / 32;
 constexpr int kChunk = 65536;
-constexpr int kTeams = 4;                // the CTA works as two teams of 16 warps on alternate tiles (see the kernel)
+constexpr int kTeams = 4;                // the CTA works as four teams of 8 warps, each on a tile of its own (see the kernel)
 constexpr int kTeamThreads = kLzThreads / kTeams;
 constexpr int kTeamWarps = kTeamThreads / 32;
 constexpr int kTile = 2048;
@@ -262,7 +268,7 @@ DSG_D uint32_t load4(const uint8_t *p) {
   return __funnelshift_r(lo, hi, 8 * m);
 }
 
-// Block-wide exclusive scan of one value per thread (512 threads). Returns the exclusive prefix and the
+// Block-wide exclusive scan of one value per thread (all kLzThreads threads). Returns the exclusive prefix and the
 // block total through *total. `scratch` has >= 17 words. Two barriers.
 DSG_D uint32_t block_exclusive_scan(uint32_t v, uint32_t *scratch, uint32_t *total) {
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -291,7 +297,7 @@ DSG_D uint32_t block_exclusive_scan(uint32_t v, uint32_t *scratch, uint32_t *tot
   return r;
 }
 
-// The same scan over the threads of a group (a team: 16 warps, its own named barrier). `scratch` >= 17 words.
+// The same scan over the threads of a group (a team: 8 warps, its own named barrier). `scratch` >= 17 words.
 DSG_D uint32_t group_exclusive_scan(uint32_t v, uint32_t *scratch, uint32_t *total, const LzGroup &g) {
   const uint32_t lane = (uint32_t)g.tid & 31, warp = (uint32_t)g.tid >> 5, nw = (uint32_t)g.n >> 5;
   uint32_t x = v;
@@ -1344,14 +1350,14 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
     chunk_flatness(P.in, P.len, cs, chunk_len, reinterpret_cast<uint32_t *>(s_work), &s_misc[kMFlat]);  // barriers inside
     __syncthreads();
 
-    // ---- tiles: a two-stage pipeline over two teams -----------------------------------------------------------
-    // Team k (16 warps) owns the tiles t = k, k+2, ...; for each it runs stage A (load, hash, shallow search) and
-    // stage B (parse / deep search rounds, final parse, token emission). Hashing must follow the hashing of tile
-    // t-1 and stage B the emission of tile t-1 (token order, the carried parse position), both done by the other
-    // team: two hand-off barriers per direction. So while one team is in stage B of tile t the other is in stage A
-    // of tile t+1, and the long tails of the search phases (the last few chains of a tile: 40 % of the phase with
-    // one tile in flight) are filled with the other team's work. The ring holds the 32 KiB window plus both tiles:
-    // loading tile t+1 overwrites only bytes that lie beyond the window of every position of tile t.
+    // ---- tiles: a pipeline over four teams ---------------------------------------------------------------------
+    // A team (8 warps) runs, for the tile it holds, stage A (load, hash, shallow search), stage B (parse / deep search
+    // rounds) and stage C (final parse, token emission). Hashing must follow the hashing of tile t-1 and stage C the
+    // emission of tile t-1 (token order, the carried parse position), each done by whichever team holds that tile: one
+    // signal per tile and direction. So while one team is in stage B of tile t the others are in other stages of the
+    // tiles around it, and the long tails of the search phases (the last few chains of a tile: 40 % of the phase with
+    // one tile in flight) are filled with their work. The ring holds the 32 KiB window plus one tile per team:
+    // loading tile t overwrites only bytes that lie beyond the window of every tile that is still in flight.
     const int ntiles = (chunk_len + kTile - 1) / kTile;
     // every team has a first tile, so the CTA-wide barrier behind it is reached by all threads
     const bool flat_candidate = s_misc[kMFlat] != 0u && ntiles >= kTeams;
