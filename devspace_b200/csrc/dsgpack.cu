@@ -343,12 +343,13 @@ bool lz_geometry(const dsg_ctx *ctx, uint64_t len, LzGeometry &G) {
   // Chunk size: the largest of 64 / 128 / 256 KiB that still leaves every SM eight chunks (see kMaxChunk).
   uint32_t chunk_bytes = kChunk;
   while (chunk_bytes < (uint32_t)kMaxChunk && len / (2ull * chunk_bytes) >= 8ull * (uint64_t)ctx->sm_count) chunk_bytes *= 2;
-  // Small inputs: a call lasts as long as its slowest SM, i.e. a whole number of chunk times (1.2 ms per 64 KiB chunk).
-  // With fewer 64 KiB chunks than SMs the chunks shrink to 32 KiB (measured on the B200: +0.4 % output on token-like
-  // text, each chunk carries its own Huffman tables and sync marker; a 4 MB tree 73 x -> 110 x the CPU path), below
-  // 128 KiB -- a change set of a few files, where the call is latency and 2 % of the output is a few hundred bytes --
-  // to 16 KiB. Above that more, smaller chunks only add dictionary builds (16 MB: slower with 32 KiB chunks).
-  if (len < (uint64_t)kChunk * (uint64_t)ctx->sm_count) chunk_bytes = len <= (128u << 10) ? kMinChunk : 2 * kMinChunk;
+  // Small inputs: a call lasts as long as its slowest SM, i.e. a whole number of chunk times (1.2 ms per 64 KiB chunk,
+  // 0.6 ms per 32 KiB one). While the input has no more 32 KiB chunks than there are SMs, halving the chunks halves the
+  // call (measured on the B200: a 4 MB tree 73 x -> 110 x the CPU path, +0.4 % output on token-like text: each chunk
+  // carries its own Huffman tables and sync marker); beyond that it only adds a second wave of chunks and dictionary
+  // builds (16 MB: slower), so 64 KiB chunks stay. Below 128 KiB -- a change set of a few files, where the call is
+  // latency and 2 % of the output is a few hundred bytes -- the chunks are 16 KiB.
+  if (len <= (uint64_t)(2 * kMinChunk) * (uint64_t)ctx->sm_count) chunk_bytes = len <= (128u << 10) ? kMinChunk : 2 * kMinChunk;
   if (o.lz_chunk_units == 1 || o.lz_chunk_units == 2 || o.lz_chunk_units == 4) chunk_bytes = o.lz_chunk_units * kChunk;
   // Runs of run_chunks big chunks first (long runs amortise hashing the dictionary); the last half run per SM is cut
   // into 64 KiB chunks and handed out one by one, so that the CTAs finish within a millisecond of each other.
