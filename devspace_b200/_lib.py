@@ -14,7 +14,7 @@ DSG_E_ARG, DSG_E_CUDA, DSG_E_HEADER, DSG_E_TYPEFLAG = -1, -2, -3, -4
 DSG_E_CAPACITY, DSG_E_UNCLEAN_NAME, DSG_E_NOMEM, DSG_E_RANGE, DSG_E_CORRUPT = -5, -6, -7, -8, -9
 DSG_LEVEL_STORED, DSG_LEVEL_DEFAULT = 0, 6
 DSG_F_NO_TRAILER = 1
-DSG_LZ_TAIL_SET, DSG_LZ_PROFILE = 1, 2
+DSG_LZ_TAIL_SET, DSG_LZ_PROFILE, DSG_LZ_NO_BULK = 1, 2, 4
 
 # every symbol include/dsgpack.h declares (tests check that the library exports all of them)
 SYMBOLS = [

@@ -152,6 +152,7 @@ struct LzParams {
   uint32_t *ticket;           // zeroed before launch
   uint32_t *tok_scratch;      // gridDim.x * kTokSlotWords
   unsigned long long *prof;   // optional: cycles per phase, summed over CTAs (thread 0's clock64 deltas)
+  uint32_t no_bulk;           // tuning knob: stage the tiles with plain loads instead of cp.async.bulk
 };
 
 enum { kProfLoad = 0, kProfInsert, kProfSearch, kProfParse, kProfEmit, kProfHuff, kProfSizes, kProfPack, kProfRefParse,
@@ -402,20 +403,35 @@ DSG_D void chunk_flatness(const uint8_t *in, uint64_t len, int64_t cs, int chunk
     __syncwarp();
     const int blen = chunk_len - b * kFlatBlock < kFlatBlock ? chunk_len - b * kFlatBlock : kFlatBlock;
     uint32_t n = 0;
-    for (int o = (int)lane * kFlatSampleStride; o + 16 <= blen; o += 32 * kFlatSampleStride) {
-      const int64_t g = cs + (int64_t)b * kFlatBlock + o;
-      if (g + 16 > (int64_t)len) break;
-#if defined(DSG_EMU)
-      const uint4 v = *reinterpret_cast<const uint4 *>(in + g);
-#else
-      const uint4 v = __ldg(reinterpret_cast<const uint4 *>(in + g));
-#endif
-      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    // the block's samples are four granules per lane: all loads are issued before the first histogram update (the
+    // bytes come from DRAM, nobody has touched them yet; one after the other they cost four round trips per chunk
+    // with the whole CTA waiting at the barrier behind this function)
+    constexpr int kPer = kFlatBlock / (32 * kFlatSampleStride);  // 4
+    uint4 v[kPer];
+    bool have[kPer];
 #pragma unroll
-      for (int k = 0; k < 4; k++) {
+    for (int k = 0; k < kPer; k++) {
+      const int o = ((int)lane + 32 * k) * kFlatSampleStride;
+      const int64_t g = cs + (int64_t)b * kFlatBlock + o;
+      have[k] = o + 16 <= blen && g + 16 <= (int64_t)len;
+      v[k] = make_uint4(0, 0, 0, 0);
+      if (have[k]) {
+#if defined(DSG_EMU)
+        v[k] = *reinterpret_cast<const uint4 *>(in + g);
+#else
+        v[k] = __ldg(reinterpret_cast<const uint4 *>(in + g));
+#endif
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < kPer; k++) {
+      if (!have[k]) continue;
+      const uint32_t w[4] = {v[k].x, v[k].y, v[k].z, v[k].w};
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
 #pragma unroll
         for (int j = 0; j < 4; j++) {
-          const uint32_t byte = (w[k] >> (8 * j)) & 0xffu;
+          const uint32_t byte = (w[q] >> (8 * j)) & 0xffu;
           atomicAdd(&h[byte >> 1], (byte & 1u) ? 0x10000u : 1u);
         }
       }
@@ -519,6 +535,7 @@ DSG_D bool bulk_ok(const LzParams &P, int64_t cs, int rp0, int rp1) {
   (void)P; (void)cs; (void)rp0; (void)rp1;
   return false;
 #else
+  if (P.no_bulk) return false;
   const int64_t g0 = cs + rp0, g1 = cs + rp1;
   return g0 >= 0 && g1 <= (int64_t)P.len && ((((uintptr_t)P.in) | (uint64_t)g0 | (uint64_t)g1) & 15) == 0;
 #endif
@@ -1385,16 +1402,17 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
       }
       LZ_PROF(kProfLoad);
       const uint32_t seq = seq_base + (uint32_t)t;  // t > 0: seq - 1 is the previous tile of this chunk
-      if (t > 0) sig_wait(s_sig, kSigIns + (int)((seq - 1) & (kSigRing - 1)), (seq - 1) / kSigRing);  // tile t-1 is in the chains
-      LZ_PROF(kProfWaitA);
-      if (bulk) {
+      // One warp of the team does the waiting (a waiting warp re-issues its try_wait; eight of them take issue slots
+      // from the teams that are working), the others park at the team's barrier.
+      if (g_team.tid < 32) {
+        if (t > 0) sig_wait(s_sig, kSigIns + (int)((seq - 1) & (kSigRing - 1)), (seq - 1) / kSigRing);  // tile t-1 is in the chains
 #if !defined(DSG_EMU)
-        mbar_wait(t_mbar, bulk_phase);
+        if (bulk) mbar_wait(t_mbar, bulk_phase);
 #endif
-        bulk_phase ^= 1u;
-      } else if (staged) {
-        group_sync(g_team);
       }
+      LZ_PROF(kProfWaitA);
+      if (bulk) bulk_phase ^= 1u;
+      if (staged || t > 0) group_sync(g_team);
       LZ_PROF(kProfLoad);
       insert_positions(s_data, s_prev, s_head, tile_rp, tile_rp + tile_len, lo_rp, g_team, t_scan,
                        &s_misc[kMRunStart]);  // ends with a barrier
@@ -1446,7 +1464,10 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
         LZ_PROF(kProfRefDeep);
       }
       // -- stage C: final parse and token emission, in tile order
-      if (t > 0) sig_wait(s_sig, kSigEmit + (int)((seq - 1) & (kSigRing - 1)), (seq - 1) / kSigRing);  // tile t-1 has emitted: kMStart and kMNTok are ours
+      if (t > 0) {  // tile t-1 has emitted: kMStart and kMNTok are ours
+        if (g_team.tid < 32) sig_wait(s_sig, kSigEmit + (int)((seq - 1) & (kSigRing - 1)), (seq - 1) / kSigRing);
+        group_sync(g_team);
+      }
       LZ_PROF(kProfWaitB);
       const int nxt = parse_tile_wide(t_mlen, t_bitmap, (int)s_misc[kMStart], tile_len, g_team);
       LZ_PROF(kProfParse);

@@ -422,6 +422,7 @@ int lz_launch(dsg_ctx *ctx, cudaStream_t stream, const uint8_t *d_in, uint64_t l
   P.ticket = ticket;
   P.tok_scratch = b_tok.as<uint32_t>();
   P.prof = nullptr;
+  P.no_bulk = (ctx->opts.lz_flags & DSG_LZ_NO_BULK) ? 1u : 0u;
   const bool prof_on = (ctx->opts.lz_flags & DSG_LZ_PROFILE) != 0;  // development aid: per-phase cycle counts on stderr
   if (prof_on) {
     CU(ctx->lz_prof.ensure(sizeof(unsigned long long) * kProfSlots));

@@ -107,9 +107,10 @@ class Packer:
 
     # -- plumbing -------------------------------------------------------------------------------------
     def _opts(self, chunk_units: int = 0, run_chunks: int = 0, grid: int = 0, tail_bytes: Optional[int] = None,
-              profile: bool = False) -> DsgOpts:
+              profile: bool = False, no_bulk: bool = False) -> DsgOpts:
         level, segment_bytes, flags = self._base
-        lz_flags = (_lib.DSG_LZ_TAIL_SET if tail_bytes is not None else 0) | (_lib.DSG_LZ_PROFILE if profile else 0)
+        lz_flags = ((_lib.DSG_LZ_TAIL_SET if tail_bytes is not None else 0) | (_lib.DSG_LZ_PROFILE if profile else 0)
+                    | (_lib.DSG_LZ_NO_BULK if no_bulk else 0))
         return DsgOpts(ctypes.sizeof(DsgOpts), level, segment_bytes, flags, 0, chunk_units, run_chunks, grid, lz_flags,
                        int(tail_bytes or 0))
 

@@ -95,6 +95,7 @@ typedef struct dsg_opts {
 #define DSG_F_NO_TRAILER 1u /* omit the 1024-byte tar trailer: for every shard but the last */
 #define DSG_LZ_TAIL_SET 1u  /* lz_tail_bytes is meaningful (0 is a valid value)                             */
 #define DSG_LZ_PROFILE 2u   /* per-phase cycle counts of the level-6 kernel on stderr (development aid)     */
+#define DSG_LZ_NO_BULK 4u   /* stage the tiles with plain loads instead of cp.async.bulk (measurement aid)  */
 
 /* Per-call timing and size counters (bench.py reads them; times are CUDA-event milliseconds). */
 typedef struct dsg_stats {
