@@ -520,27 +520,48 @@ gz_tails_plain(const GzUnit *__restrict__ units, uint32_t nunits, const uint16_t
 __global__ void __launch_bounds__(1024)
 gz_tails_kernel(const GzUnit *__restrict__ units, uint32_t nunits, const uint16_t *__restrict__ out16,
                 uint8_t *__restrict__ out, const uint32_t *__restrict__ needs_fix) {
-  for (uint32_t i = 0; i < nunits; i++) {
-    if (needs_fix[i] == 0) continue;  // uniform
-    const GzUnit u = units[i];
-    const uint32_t t0 = u.out_len > kGzWindow ? u.out_len - kGzWindow : 0;
-    // Every reference of this tail points in front of the unit, never into the tail itself: all loads first (32
-    // independent symbol loads and gathers per thread in flight), then the stores. A load-store loop would serialise
-    // on the possible aliasing of `out` with itself: one L2 round trip per symbol.
-    uint32_t v[32];
-#pragma unroll
-    for (int k = 0; k < 32; k++) {
-      const uint32_t j = t0 + (uint32_t)k * 1024u + threadIdx.x;
-      v[k] = j < u.out_len ? out16[u.out_off + j] : 0u;
-    }
-#pragma unroll
-    for (int k = 0; k < 32; k++)
-      if (v[k] >= 256) v[k] = 256u + out[u.out_off - kGzWindow + (v[k] - 256)];
-#pragma unroll
-    for (int k = 0; k < 32; k++)
-      if (v[k] >= 256) out[u.out_off + t0 + (uint32_t)k * 1024u + threadIdx.x] = (uint8_t)(v[k] - 256);
-    __threadfence_block();
+  // unit descriptors and flags come in batches through shared memory: per unit only its symbols and the window bytes
+  // are fetched from global memory (a descriptor read per unit is one more dependent L2 round trip in the serial chain)
+  __shared__ uint64_t s_off[1024];
+  __shared__ uint32_t s_len[1024];  // 0 = nothing to do for this unit
+  for (uint32_t base = 0; base < nunits; base += 1024) {
     __syncthreads();
+    {
+      const uint32_t i = base + threadIdx.x;
+      uint32_t len = 0;
+      uint64_t off = 0;
+      if (i < nunits && needs_fix[i]) {
+        const GzUnit u = units[i];
+        len = u.out_len;
+        off = u.out_off;
+      }
+      s_off[threadIdx.x] = off;
+      s_len[threadIdx.x] = len;
+    }
+    __syncthreads();
+    const uint32_t cnt = nunits - base < 1024 ? nunits - base : 1024;
+    for (uint32_t k0 = 0; k0 < cnt; k0++) {
+      const uint32_t out_len = s_len[k0];
+      if (out_len == 0) continue;  // uniform
+      const uint64_t out_off = s_off[k0];
+      const uint32_t t0 = out_len > kGzWindow ? out_len - kGzWindow : 0;
+      // Every reference of this tail points in front of the unit, never into the tail itself: all loads first (32
+      // independent symbol loads and gathers per thread in flight), then the stores. A load-store loop would serialise
+      // on the possible aliasing of `out` with itself: one L2 round trip per symbol.
+      uint32_t v[32];
+#pragma unroll
+      for (int k = 0; k < 32; k++) {
+        const uint32_t j = t0 + (uint32_t)k * 1024u + threadIdx.x;
+        v[k] = j < out_len ? out16[out_off + j] : 0u;
+      }
+#pragma unroll
+      for (int k = 0; k < 32; k++)
+        if (v[k] >= 256) v[k] = 256u + out[out_off - kGzWindow + (v[k] - 256)];
+#pragma unroll
+      for (int k = 0; k < 32; k++)
+        if (v[k] >= 256) out[out_off + t0 + (uint32_t)k * 1024u + threadIdx.x] = (uint8_t)(v[k] - 256);
+      __syncthreads();  // the tail is visible to the whole CTA before the next unit reads its window
+    }
   }
 }
 
