@@ -1488,7 +1488,7 @@ int gunzip_device(dsg_ctx *ctx, const uint8_t *d_in, uint64_t n, uint8_t *d_out,
   const uint32_t max_units = ncand + 16, max_members = 65536;
   CU(ctx->gz_units.ensure(sizeof(GzUnit) * (size_t)max_units));
   CU(ctx->gz_members.ensure(sizeof(GzMember) * (size_t)max_members));
-  CU(ctx->gz_misc.ensure(sizeof(GzSummary) + 64));
+  CU(ctx->gz_misc.ensure(sizeof(GzSummary) + 128));
   GzUnit *d_units = ctx->gz_units.as<GzUnit>();
   GzMember *d_members = ctx->gz_members.as<GzMember>();
   GzSummary *d_sum = ctx->gz_misc.as<GzSummary>();
@@ -1520,10 +1520,31 @@ int gunzip_device(dsg_ctx *ctx, const uint8_t *d_in, uint64_t n, uint8_t *d_out,
   LAUNCH_CHECK();
   CU(ctx->gz_counts.ensure(sizeof(uint32_t) * (size_t)S.nunits + 64));  // (the scan counters are done with)
   uint32_t *d_fix = ctx->gz_counts.as<uint32_t>();
-  gz_tails_plain<<<S.nunits, 256, 0, st>>>(d_units, S.nunits, d_sym, d_out, d_fix);
+  gz_tails_plain<<<S.nunits, 256, 0, st>>>(d_in, d_units, S.nunits, d_sym, d_out, d_fix);
   LAUNCH_CHECK();
-  gz_tails_kernel<<<1, 1024, 0, st>>>(d_units, S.nunits, d_sym, d_out, d_fix);
-  LAUNCH_CHECK();
+  {
+    // parallel rounds, four at a time, until no tail holds an open reference; a stream that still has some after 48
+    // rounds, or whose open tails stop halving, finishes in the serial kernel
+    uint32_t *d_open = d_err + 1;  // 8 counters behind the error word
+    uint32_t open_units = 1, before = 0xffffffffu;
+    for (int batch = 0; batch < 12 && open_units; batch++) {
+      CU(cudaMemsetAsync(d_open, 0, sizeof(uint32_t) * 4, st));
+      for (int r = 0; r < 4; r++) {
+        gz_tails_round<<<S.nunits, 256, 0, st>>>(d_units, S.nunits, d_sym, d_out, d_fix, d_open + r);
+        LAUNCH_CHECK();
+      }
+      CU(cudaMemcpyAsync(&open_units, d_open + 3, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+      CU(cudaStreamSynchronize(st));
+      // rounds that do not at least halve the open tails are a long chain working its way down the stream one unit
+      // per round (template-like text: a phrase handed down through every chunk): the serial kernel is faster there
+      if (open_units > before / 2) break;
+      before = open_units;
+    }
+    if (open_units) {
+      gz_tails_kernel<<<1, 1024, 0, st>>>(d_units, S.nunits, d_sym, d_out, d_fix);
+      LAUNCH_CHECK();
+    }
+  }
   gz_bodies_kernel<<<S.nunits, 256, 0, st>>>(d_units, S.nunits, d_sym, d_out);
   LAUNCH_CHECK();
   toc(ctx, kTimDeflate);

@@ -24,8 +24,9 @@
 //                                   (the compressor's dictionary), which another thread is producing at the same time:
 //                                   the decode writes 16-bit symbols -- a byte, or 256 + index into that window --
 //                                   and copies symbols, so that window references propagate through copies of copies;
-//   gz_tails_kernel                 one CTA, units in order: resolves the last 32 KiB of every unit (its window
-//                                   references point into the tails before it, which are final by then);
+//   gz_tails_plain / gz_tails_round the last 32 KiB of every unit: plain bytes at once, window references in parallel
+//                                   rounds (a reference whose source in the tails before it is a byte by now);
+//   gz_tails_kernel                 one CTA, units in order: whatever the rounds left open (long chains of copies);
 //   gz_bodies_kernel                all units in parallel: resolves the rest against the finished tails;
 //   gz_stored_copy_kernel           stored blocks straight from the input.
 // CRC32 and ISIZE of every member are checked by the caller with the CRC kernels of crc32.cuh.
@@ -499,15 +500,18 @@ gz_stored_copy_kernel(const uint8_t *__restrict__ in, const GzUnit *__restrict__
 // before the unit -- the tails of the units before it, final by the time this unit's turn comes. (As one sequential
 // kernel over every unit and every tail symbol this step was 118 of the 150 ms of a 476 MB stream.)
 __global__ void __launch_bounds__(256)
-gz_tails_plain(const GzUnit *__restrict__ units, uint32_t nunits, const uint16_t *__restrict__ out16,
-               uint8_t *__restrict__ out, uint32_t *__restrict__ needs_fix) {
+gz_tails_plain(const uint8_t *__restrict__ in, const GzUnit *__restrict__ units, uint32_t nunits,
+               uint16_t *__restrict__ out16, uint8_t *__restrict__ out, uint32_t *__restrict__ needs_fix) {
   const uint32_t i = blockIdx.x;
   if (i >= nunits) return;
   const GzUnit u = units[i];
   if (threadIdx.x == 0) needs_fix[i] = 0;
   __syncthreads();
-  if (u.kind != kGzCompressed) return;
   const uint32_t t0 = u.out_len > kGzWindow ? u.out_len - kGzWindow : 0;
+  if (u.kind != kGzCompressed) {  // a stored block's tail as symbols too: the rounds below look sources up in out16
+    for (uint32_t j = t0 + threadIdx.x; j < u.out_len; j += 256) out16[u.out_off + j] = in[u.in_off + j];
+    return;
+  }
   bool any = false;
   for (uint32_t j = t0 + threadIdx.x; j < u.out_len; j += 256) {
     const uint32_t v = out16[u.out_off + j];
@@ -515,6 +519,42 @@ gz_tails_plain(const GzUnit *__restrict__ units, uint32_t nunits, const uint16_t
     else any = true;
   }
   if (any) needs_fix[i] = 1;
+}
+
+// One round over the flagged tails, all at once: a window reference whose source symbol (in the tails in front of the
+// unit) is a plain byte by now becomes that byte; one whose source is still a reference waits for the next round. The
+// number of rounds is the longest chain of copies ACROSS units (a handful; a phrase handed down through thousands of
+// chunks would need thousands: the caller stops after a fixed number of rounds and leaves the rest to the serial
+// kernel below). A 16-bit symbol is read and written whole, and it only ever changes from reference to byte, so a
+// racing reader sees one of two valid states.
+__global__ void __launch_bounds__(256)
+gz_tails_round(const GzUnit *__restrict__ units, uint32_t nunits, uint16_t *out16, uint8_t *__restrict__ out,
+               uint32_t *__restrict__ needs_fix, uint32_t *__restrict__ open_units) {
+  const uint32_t i = blockIdx.x;
+  if (i >= nunits || needs_fix[i] == 0) return;
+  const GzUnit u = units[i];
+  const uint32_t t0 = u.out_len > kGzWindow ? u.out_len - kGzWindow : 0;
+  __shared__ uint32_t left;
+  if (threadIdx.x == 0) left = 0;
+  __syncthreads();
+  uint32_t mine = 0;
+  for (uint32_t j = t0 + threadIdx.x; j < u.out_len; j += 256) {
+    const uint32_t v = out16[u.out_off + j];
+    if (v < 256) continue;
+    const uint32_t sv = *reinterpret_cast<volatile uint16_t *>(out16 + (u.out_off - kGzWindow + (v - 256)));
+    if (sv < 256) {
+      out16[u.out_off + j] = (uint16_t)sv;
+      out[u.out_off + j] = (uint8_t)sv;
+    } else {
+      mine++;
+    }
+  }
+  if (mine) atomicAdd(&left, mine);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (left == 0) needs_fix[i] = 0;
+    else atomicAdd(open_units, 1u);
+  }
 }
 
 __global__ void __launch_bounds__(1024)

@@ -184,7 +184,7 @@ int emu_huff_lengths(const uint32_t *freq, int n, int max_bits, uint8_t *lens) {
 // bodies. Returns 0, DSG_E_ARG (not a stream of this library), DSG_E_CAPACITY or DSG_E_CORRUPT (second pass differs);
 // crcs_ok = every member's CRC32 matches (checked here with the serial table-free recurrence, test infrastructure).
 int emu_gunzip(const uint8_t *in, uint64_t n, uint8_t *out, uint64_t cap, uint64_t *out_len, uint32_t *nunits_out,
-               uint32_t *nmembers_out, uint32_t *ncand_out) {
+               uint32_t *nmembers_out, uint32_t *ncand_out, uint32_t rounds) {
   *out_len = 0;
   if (n < 20) return DSG_E_ARG;
   const uint32_t ncta = (uint32_t)((n + kGzScanCta - 1) / kGzScanCta);
@@ -224,8 +224,17 @@ int emu_gunzip(const uint8_t *in, uint64_t n, uint8_t *out, uint64_t cap, uint64
   if (err) return DSG_E_CORRUPT;
   emu::launch(dim3(S.nunits), dim3(256), 0, [&] { gz_stored_copy_kernel(in, units.data(), S.nunits, out); });
   std::vector<uint32_t> fix(S.nunits, 7);
-  emu::launch(dim3(S.nunits), dim3(256), 0, [&] { gz_tails_plain(units.data(), S.nunits, sym.data(), out, fix.data()); });
-  emu::launch(dim3(1), dim3(1024), 0, [&] { gz_tails_kernel(units.data(), S.nunits, sym.data(), out, fix.data()); });
+  emu::launch(dim3(S.nunits), dim3(256), 0,
+              [&] { gz_tails_plain(in, units.data(), S.nunits, sym.data(), out, fix.data()); });
+  // `rounds` parallel rounds (the host's limit is 48; the tests also run with few, so that the serial kernel is reached)
+  uint32_t open_units = 1;
+  for (uint32_t r = 0; r < rounds && open_units; r++) {
+    open_units = 0;
+    emu::launch(dim3(S.nunits), dim3(256), 0,
+                [&] { gz_tails_round(units.data(), S.nunits, sym.data(), out, fix.data(), &open_units); });
+  }
+  if (open_units)
+    emu::launch(dim3(1), dim3(1024), 0, [&] { gz_tails_kernel(units.data(), S.nunits, sym.data(), out, fix.data()); });
   emu::launch(dim3(S.nunits), dim3(256), 0, [&] { gz_bodies_kernel(units.data(), S.nunits, sym.data(), out); });
   return 0;
 }
