@@ -33,7 +33,7 @@ DSG_MULTI_ONE_MEMBER = 1
 
 class DsgOpts(ctypes.Structure):
     _fields_ = [("struct_size", c_uint32), ("level", c_int32), ("segment_bytes", c_uint64), ("flags", c_uint32),
-                ("reserved", c_uint32), ("lz_chunk_units", c_uint32), ("lz_run_chunks", c_uint32),
+                ("gunzip_batch_mib", c_uint32), ("lz_chunk_units", c_uint32), ("lz_run_chunks", c_uint32),
                 ("lz_grid", c_uint32), ("lz_flags", c_uint32), ("lz_tail_bytes", c_uint64)]
 
 

@@ -1510,27 +1510,40 @@ int gunzip_device(dsg_ctx *ctx, const uint8_t *d_in, uint64_t n, uint8_t *d_out,
     return fail(ctx, DSG_E_CAPACITY, "output needs %llu bytes, capacity %llu", (unsigned long long)S.total_out,
                 (unsigned long long)out_cap);
   if (S.nunits == 0) return DSG_OK;
-  // 4. decode into 16-bit symbols, stored blocks straight to the output, then resolve the window references
-  CU(ctx->gz_sym.ensure(sizeof(uint16_t) * (size_t)S.total_out + 64));
+  // 4. decode into 16-bit symbols, stored blocks straight to the output, then resolve the window references -- in
+  // batches of consecutive units, so that the symbol scratch (2 bytes per output byte) stays bounded for streams of
+  // tens of GB: a batch's references into the bytes in front of it find them final in `out`
+  std::vector<GzUnit> h_units(S.nunits);
+  CU(cudaMemcpyAsync(h_units.data(), d_units, sizeof(GzUnit) * S.nunits, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  const uint64_t batch_out = (ctx->opts.gunzip_batch_mib ? (uint64_t)ctx->opts.gunzip_batch_mib : 2048ull) << 20;
+  CU(ctx->gz_sym.ensure(sizeof(uint16_t) * (size_t)(std::min<uint64_t>(S.total_out, batch_out) + kGzMaxUnitOut) + 64));
   uint16_t *d_sym = ctx->gz_sym.as<uint16_t>();
   tic(ctx, kTimDeflate);
-  gz_decode_kernel<<<(S.nunits + kGzWarpsPerCta - 1) / kGzWarpsPerCta, 32 * kGzWarpsPerCta, 0, st>>>(d_in, n, d_units, S.nunits, d_sym, d_err);
-  LAUNCH_CHECK();
   gz_stored_copy_kernel<<<S.nunits, 256, 0, st>>>(d_in, d_units, S.nunits, d_out);
   LAUNCH_CHECK();
-  CU(ctx->gz_counts.ensure(sizeof(uint32_t) * (size_t)S.nunits + 64));  // (the scan counters are done with)
-  uint32_t *d_fix = ctx->gz_counts.as<uint32_t>();
-  gz_tails_plain<<<S.nunits, 256, 0, st>>>(d_in, d_units, S.nunits, d_sym, d_out, d_fix);
-  LAUNCH_CHECK();
-  {
+  uint32_t u0 = 0, nbatches = 0;
+  while (u0 < S.nunits) {
+    const uint64_t base = h_units[u0].out_off;
+    uint32_t u1 = u0 + 1;
+    while (u1 < S.nunits && h_units[u1].out_off + h_units[u1].out_len - base <= batch_out) u1++;
+    const uint32_t nb = u1 - u0;
+    const GzUnit *bu = d_units + u0;
+    nbatches++;
+    gz_decode_kernel<<<(nb + kGzWarpsPerCta - 1) / kGzWarpsPerCta, 32 * kGzWarpsPerCta, 0, st>>>(d_in, n, bu, nb, d_sym, base, d_err);
+    LAUNCH_CHECK();
+    CU(ctx->gz_counts.ensure(sizeof(uint32_t) * (size_t)nb + 64));  // (the scan counters are done with)
+    uint32_t *d_fix = ctx->gz_counts.as<uint32_t>();
+    gz_tails_plain<<<nb, 256, 0, st>>>(d_in, bu, nb, d_sym, base, d_out, d_fix);
+    LAUNCH_CHECK();
     // parallel rounds, four at a time, until no tail holds an open reference; a stream that still has some after 48
     // rounds, or whose open tails stop halving, finishes in the serial kernel
-    uint32_t *d_open = d_err + 1;  // 8 counters behind the error word
+    uint32_t *d_open = d_err + 1;  // 4 counters behind the error word
     uint32_t open_units = 1, before = 0xffffffffu;
     for (int batch = 0; batch < 12 && open_units; batch++) {
       CU(cudaMemsetAsync(d_open, 0, sizeof(uint32_t) * 4, st));
       for (int r = 0; r < 4; r++) {
-        gz_tails_round<<<S.nunits, 256, 0, st>>>(d_units, S.nunits, d_sym, d_out, d_fix, d_open + r);
+        gz_tails_round<<<nb, 256, 0, st>>>(bu, nb, d_sym, base, d_out, d_fix, d_open + r);
         LAUNCH_CHECK();
       }
       CU(cudaMemcpyAsync(&open_units, d_open + 3, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
@@ -1541,12 +1554,13 @@ int gunzip_device(dsg_ctx *ctx, const uint8_t *d_in, uint64_t n, uint8_t *d_out,
       before = open_units;
     }
     if (open_units) {
-      gz_tails_kernel<<<1, 1024, 0, st>>>(d_units, S.nunits, d_sym, d_out, d_fix);
+      gz_tails_kernel<<<1, 1024, 0, st>>>(bu, nb, d_sym, base, d_out, d_fix);
       LAUNCH_CHECK();
     }
+    gz_bodies_kernel<<<nb, 256, 0, st>>>(bu, nb, d_sym, base, d_out);
+    LAUNCH_CHECK();
+    u0 = u1;
   }
-  gz_bodies_kernel<<<S.nunits, 256, 0, st>>>(d_units, S.nunits, d_sym, d_out);
-  LAUNCH_CHECK();
   toc(ctx, kTimDeflate);
   uint32_t h_err = 0;
   CU(cudaMemcpyAsync(&h_err, d_err, sizeof h_err, cudaMemcpyDeviceToHost, st));

@@ -469,7 +469,7 @@ __global__ void gz_chain_kernel(const uint8_t *in, uint64_t n, const uint64_t *c
 
 __global__ void __launch_bounds__(32 * kGzWarpsPerCta)
 gz_decode_kernel(const uint8_t *__restrict__ in, uint64_t n, const GzUnit *__restrict__ units, uint32_t nunits,
-                 uint16_t *__restrict__ out16, uint32_t *__restrict__ error) {
+                 uint16_t *__restrict__ out16, uint64_t sym_base, uint32_t *__restrict__ error) {
   __shared__ uint16_t s_tab[kGzWarpsPerCta][(1 << kGzLitBits) + (1 << kGzDistBits)];
   const uint32_t i = blockIdx.x * kGzWarpsPerCta + (threadIdx.x >> 5);  // one warp per unit
   if (i >= nunits) return;
@@ -478,7 +478,7 @@ gz_decode_kernel(const uint8_t *__restrict__ in, uint64_t n, const GzUnit *__res
   uint16_t *tab = s_tab[threadIdx.x >> 5];
   uint32_t len;
   uint64_t end;
-  const uint32_t k = gz_decode_unit<true>(in, n, u.in_off, u.win_avail, out16 + u.out_off, &len, &end, threadIdx.x & 31,
+  const uint32_t k = gz_decode_unit<true>(in, n, u.in_off, u.win_avail, out16 + (u.out_off - sym_base), &len, &end, threadIdx.x & 31,
                                           tab, tab + (1 << kGzLitBits));
   if ((k != kGzCompressed || len != u.out_len) && (threadIdx.x & 31) == 0) atomicExch(error, i + 1);
 }
@@ -501,7 +501,8 @@ gz_stored_copy_kernel(const uint8_t *__restrict__ in, const GzUnit *__restrict__
 // kernel over every unit and every tail symbol this step was 118 of the 150 ms of a 476 MB stream.)
 __global__ void __launch_bounds__(256)
 gz_tails_plain(const uint8_t *__restrict__ in, const GzUnit *__restrict__ units, uint32_t nunits,
-               uint16_t *__restrict__ out16, uint8_t *__restrict__ out, uint32_t *__restrict__ needs_fix) {
+               uint16_t *__restrict__ out16, uint64_t sym_base, uint8_t *__restrict__ out,
+               uint32_t *__restrict__ needs_fix) {
   const uint32_t i = blockIdx.x;
   if (i >= nunits) return;
   const GzUnit u = units[i];
@@ -509,12 +510,12 @@ gz_tails_plain(const uint8_t *__restrict__ in, const GzUnit *__restrict__ units,
   __syncthreads();
   const uint32_t t0 = u.out_len > kGzWindow ? u.out_len - kGzWindow : 0;
   if (u.kind != kGzCompressed) {  // a stored block's tail as symbols too: the rounds below look sources up in out16
-    for (uint32_t j = t0 + threadIdx.x; j < u.out_len; j += 256) out16[u.out_off + j] = in[u.in_off + j];
+    for (uint32_t j = t0 + threadIdx.x; j < u.out_len; j += 256) out16[u.out_off - sym_base + j] = in[u.in_off + j];
     return;
   }
   bool any = false;
   for (uint32_t j = t0 + threadIdx.x; j < u.out_len; j += 256) {
-    const uint32_t v = out16[u.out_off + j];
+    const uint32_t v = out16[u.out_off - sym_base + j];
     if (v < 256) out[u.out_off + j] = (uint8_t)v;
     else any = true;
   }
@@ -528,7 +529,7 @@ gz_tails_plain(const uint8_t *__restrict__ in, const GzUnit *__restrict__ units,
 // kernel below). A 16-bit symbol is read and written whole, and it only ever changes from reference to byte, so a
 // racing reader sees one of two valid states.
 __global__ void __launch_bounds__(256)
-gz_tails_round(const GzUnit *__restrict__ units, uint32_t nunits, uint16_t *out16, uint8_t *__restrict__ out,
+gz_tails_round(const GzUnit *__restrict__ units, uint32_t nunits, uint16_t *out16, uint64_t sym_base, uint8_t *out,
                uint32_t *__restrict__ needs_fix, uint32_t *__restrict__ open_units) {
   const uint32_t i = blockIdx.x;
   if (i >= nunits || needs_fix[i] == 0) return;
@@ -539,11 +540,12 @@ gz_tails_round(const GzUnit *__restrict__ units, uint32_t nunits, uint16_t *out1
   __syncthreads();
   uint32_t mine = 0;
   for (uint32_t j = t0 + threadIdx.x; j < u.out_len; j += 256) {
-    const uint32_t v = out16[u.out_off + j];
+    const uint32_t v = out16[u.out_off - sym_base + j];
     if (v < 256) continue;
-    const uint32_t sv = *reinterpret_cast<volatile uint16_t *>(out16 + (u.out_off - kGzWindow + (v - 256)));
+    const uint64_t src = u.out_off - kGzWindow + (v - 256);  // a source in front of this batch of units is final
+    const uint32_t sv = src < sym_base ? (uint32_t)out[src] : *reinterpret_cast<volatile uint16_t *>(out16 + (src - sym_base));
     if (sv < 256) {
-      out16[u.out_off + j] = (uint16_t)sv;
+      out16[u.out_off - sym_base + j] = (uint16_t)sv;
       out[u.out_off + j] = (uint8_t)sv;
     } else {
       mine++;
@@ -559,7 +561,7 @@ gz_tails_round(const GzUnit *__restrict__ units, uint32_t nunits, uint16_t *out1
 
 __global__ void __launch_bounds__(1024)
 gz_tails_kernel(const GzUnit *__restrict__ units, uint32_t nunits, const uint16_t *__restrict__ out16,
-                uint8_t *__restrict__ out, const uint32_t *__restrict__ needs_fix) {
+                uint64_t sym_base, uint8_t *__restrict__ out, const uint32_t *__restrict__ needs_fix) {
   // unit descriptors and flags come in batches through shared memory: per unit only its symbols and the window bytes
   // are fetched from global memory (a descriptor read per unit is one more dependent L2 round trip in the serial chain)
   __shared__ uint64_t s_off[1024];
@@ -592,7 +594,7 @@ gz_tails_kernel(const GzUnit *__restrict__ units, uint32_t nunits, const uint16_
 #pragma unroll
       for (int k = 0; k < 32; k++) {
         const uint32_t j = t0 + (uint32_t)k * 1024u + threadIdx.x;
-        v[k] = j < out_len ? out16[out_off + j] : 0u;
+        v[k] = j < out_len ? out16[out_off - sym_base + j] : 0u;
       }
 #pragma unroll
       for (int k = 0; k < 32; k++)
@@ -608,14 +610,14 @@ gz_tails_kernel(const GzUnit *__restrict__ units, uint32_t nunits, const uint16_
 // One CTA per unit: everything in front of the tail.
 __global__ void __launch_bounds__(256)
 gz_bodies_kernel(const GzUnit *__restrict__ units, uint32_t nunits, const uint16_t *__restrict__ out16,
-                 uint8_t *__restrict__ out) {
+                 uint64_t sym_base, uint8_t *__restrict__ out) {
   const uint32_t i = blockIdx.x;
   if (i >= nunits) return;
   const GzUnit u = units[i];
   if (u.kind != kGzCompressed || u.out_len <= kGzWindow) return;
   const uint32_t body = u.out_len - kGzWindow;
   for (uint32_t j = threadIdx.x; j < body; j += 256) {
-    const uint32_t v = out16[u.out_off + j];
+    const uint32_t v = out16[u.out_off - sym_base + j];
     out[u.out_off + j] = v < 256 ? (uint8_t)v : out[u.out_off - kGzWindow + (v - 256)];
   }
 }

@@ -82,7 +82,7 @@ typedef struct dsg_opts {
   uint64_t segment_bytes;  /* tar-stream bytes per pipeline segment (0 = a sixth of the stream,
                             * between 64 and 512 MiB)                                            */
   uint32_t flags;          /* DSG_F_*                                                                */
-  uint32_t reserved;
+  uint32_t gunzip_batch_mib; /* dsg_gunzip: decompressed MiB per batch of chunks (0 = 2048); bounds the scratch */
   /* Launch geometry of the level-6 kernel. All zero (the default) = chosen from the input size. The parity
    * tests and the profiling tools set these to reach every geometry with small inputs; a caller never has to. */
   uint32_t lz_chunk_units; /* deflate chunk = 1, 2 or 4 units of 64 KiB (0 = automatic)                    */

@@ -184,7 +184,7 @@ int emu_huff_lengths(const uint32_t *freq, int n, int max_bits, uint8_t *lens) {
 // bodies. Returns 0, DSG_E_ARG (not a stream of this library), DSG_E_CAPACITY or DSG_E_CORRUPT (second pass differs);
 // crcs_ok = every member's CRC32 matches (checked here with the serial table-free recurrence, test infrastructure).
 int emu_gunzip(const uint8_t *in, uint64_t n, uint8_t *out, uint64_t cap, uint64_t *out_len, uint32_t *nunits_out,
-               uint32_t *nmembers_out, uint32_t *ncand_out, uint32_t rounds) {
+               uint32_t *nmembers_out, uint32_t *ncand_out, uint32_t rounds, uint64_t batch_bytes) {
   *out_len = 0;
   if (n < 20) return DSG_E_ARG;
   const uint32_t ncta = (uint32_t)((n + kGzScanCta - 1) / kGzScanCta);
@@ -217,25 +217,35 @@ int emu_gunzip(const uint8_t *in, uint64_t n, uint8_t *out, uint64_t cap, uint64
   if (nmembers_out) *nmembers_out = S.nmembers;
   if (S.total_out > cap) return DSG_E_CAPACITY;
   if (S.nunits == 0) return 0;
-  std::vector<uint16_t> sym(S.total_out + 8, 0xEEEE);
-  uint32_t err = 0;
-  emu::launch(dim3((S.nunits + kGzWarpsPerCta - 1) / kGzWarpsPerCta), dim3(32 * kGzWarpsPerCta), 0,
-              [&] { gz_decode_kernel(in, n, units.data(), S.nunits, sym.data(), &err); });
-  if (err) return DSG_E_CORRUPT;
+  // batches of consecutive units, as the host does (batch_bytes == 0: one batch)
+  const uint64_t batch_out = batch_bytes ? batch_bytes : S.total_out;
+  std::vector<uint16_t> sym(std::min<uint64_t>(S.total_out, batch_out) + kGzMaxUnitOut + 8, 0xEEEE);
   emu::launch(dim3(S.nunits), dim3(256), 0, [&] { gz_stored_copy_kernel(in, units.data(), S.nunits, out); });
-  std::vector<uint32_t> fix(S.nunits, 7);
-  emu::launch(dim3(S.nunits), dim3(256), 0,
-              [&] { gz_tails_plain(in, units.data(), S.nunits, sym.data(), out, fix.data()); });
-  // `rounds` parallel rounds (the host's limit is 48; the tests also run with few, so that the serial kernel is reached)
-  uint32_t open_units = 1;
-  for (uint32_t r = 0; r < rounds && open_units; r++) {
-    open_units = 0;
-    emu::launch(dim3(S.nunits), dim3(256), 0,
-                [&] { gz_tails_round(units.data(), S.nunits, sym.data(), out, fix.data(), &open_units); });
+  uint32_t u0 = 0;
+  while (u0 < S.nunits) {
+    const uint64_t base = units[u0].out_off;
+    uint32_t u1 = u0 + 1;
+    while (u1 < S.nunits && units[u1].out_off + units[u1].out_len - base <= batch_out) u1++;
+    const uint32_t nb = u1 - u0;
+    const GzUnit *bu = units.data() + u0;
+    std::fill(sym.begin(), sym.end(), (uint16_t)0xEEEE);
+    uint32_t err = 0;
+    emu::launch(dim3((nb + kGzWarpsPerCta - 1) / kGzWarpsPerCta), dim3(32 * kGzWarpsPerCta), 0,
+                [&] { gz_decode_kernel(in, n, bu, nb, sym.data(), base, &err); });
+    if (err) return DSG_E_CORRUPT;
+    std::vector<uint32_t> fix(nb, 7);
+    emu::launch(dim3(nb), dim3(256), 0, [&] { gz_tails_plain(in, bu, nb, sym.data(), base, out, fix.data()); });
+    // `rounds` parallel rounds (the host's limit is 48; the tests also run with few, so that the serial kernel is reached)
+    uint32_t open_units = 1;
+    for (uint32_t r = 0; r < rounds && open_units; r++) {
+      open_units = 0;
+      emu::launch(dim3(nb), dim3(256), 0, [&] { gz_tails_round(bu, nb, sym.data(), base, out, fix.data(), &open_units); });
+    }
+    if (open_units)
+      emu::launch(dim3(1), dim3(1024), 0, [&] { gz_tails_kernel(bu, nb, sym.data(), base, out, fix.data()); });
+    emu::launch(dim3(nb), dim3(256), 0, [&] { gz_bodies_kernel(bu, nb, sym.data(), base, out); });
+    u0 = u1;
   }
-  if (open_units)
-    emu::launch(dim3(1), dim3(1024), 0, [&] { gz_tails_kernel(units.data(), S.nunits, sym.data(), out, fix.data()); });
-  emu::launch(dim3(S.nunits), dim3(256), 0, [&] { gz_bodies_kernel(units.data(), S.nunits, sym.data(), out); });
   return 0;
 }
 

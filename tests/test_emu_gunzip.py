@@ -19,7 +19,7 @@ def member(raw_deflate: bytes, data: bytes) -> bytes:
     return HDR + raw_deflate + struct.pack("<II", zlib.crc32(data), len(data) & 0xFFFFFFFF)
 
 
-def emu_gunzip(blob: bytes, cap=None, rounds=48):
+def emu_gunzip(blob: bytes, cap=None, rounds=48, batch=0):
     L = helpers.emu_lib()
     a = np.frombuffer(blob, np.uint8)
     cap = len(blob) * 60 + 1024 if cap is None else cap
@@ -27,7 +27,7 @@ def emu_gunzip(blob: bytes, cap=None, rounds=48):
     n, nu, nm, nc = ctypes.c_uint64(), ctypes.c_uint32(), ctypes.c_uint32(), ctypes.c_uint32()
     rc = L.emu_gunzip(ctypes.c_void_p(a.ctypes.data), ctypes.c_uint64(a.size), ctypes.c_void_p(out.ctypes.data),
                       ctypes.c_uint64(cap), ctypes.byref(n), ctypes.byref(nu), ctypes.byref(nm), ctypes.byref(nc),
-                      ctypes.c_uint32(rounds))
+                      ctypes.c_uint32(rounds), ctypes.c_uint64(batch))
     return rc, out[: n.value].tobytes() if rc == 0 else b"", n.value, nu.value, nm.value, nc.value
 
 
@@ -53,6 +53,7 @@ def test_emulated_gunzip_of_emulated_deflate(name):
         assert rc == 0 and out == data and nmembers == 1, (name, kw, rc, n, len(data))
         for rounds in (0, 1):                     # the serial kernel takes what the parallel rounds leave open
             assert emu_gunzip(blob, rounds=rounds)[1] == data, (name, kw, rounds)
+        assert emu_gunzip(blob, batch=70_000)[1] == data     # batches of one or two units: references across batches
         if len(data) > 70_000:
             assert nunits >= 2
 

@@ -57,6 +57,8 @@ def test_gunzip_small_trees_every_geometry(tree):
             assert p.gunzip(blob) == ref, (tree, kw)
     with Packer(level=0) as p:                                  # stored blocks only
         assert p.gunzip(p.pack(man)) == ref
+    with Packer(level=6, gunzip_batch_mib=1) as p:              # many batches: references across batch boundaries
+        assert p.gunzip(p.pack(man)) == ref
 
 
 def test_gunzip_members_of_several_shards_and_the_stitched_member():
