@@ -71,3 +71,20 @@ def test_multi_pack_reports_errors_and_small_buffers():
         with pytest.raises(DsgError):
             mp.pack(bad)
         assert gzip.decompress(mp.pack(man)) == oracle.tar_stream(helpers.manifest_entries(man, 0, man.n))
+
+
+def test_multi_pack_more_shards_than_entries():
+    """Four shards, two entries: the empty shards write empty members (header, empty final block, trailer); the stream
+    still gunzips to the oracle's tar stream, with a stock decoder and with dsg_gunzip."""
+    from devspace_b200.manifest import from_entries
+    from devspace_b200.multi import MultiPacker
+    from devspace_b200.pack import Packer
+    es = [helpers.F("a.txt", b"TestContents" * 5000), helpers.F("b.bin", helpers.rng_bytes(3, 70_000))]
+    ref = oracle.tar_stream(es)
+    with MultiPacker([0, 0, 0, 0]) as mp, Packer() as p:
+        for one in (False, True):
+            blob = mp.pack(from_entries(es), one_member=one)
+            assert gzip.decompress(blob) == ref
+            assert p.gunzip(blob) == ref
+    with MultiPacker([0, 0]) as mp:
+        assert gzip.decompress(mp.pack(from_entries([]))) == oracle.tar_stream([])
