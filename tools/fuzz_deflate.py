@@ -51,6 +51,10 @@ def main():
             p.set_lz_geometry(**geo)
             raw = p.deflate(data, level=6)
             assert zlib.decompress(raw, -15) == data, ("round trip", c, len(data), geo)
+            if c % 3 == 0:   # the downstream direction on the same stream, in small batches now and then
+                g = p.deflate(data, level=6, gzip=True)
+                p.set_lz_geometry(gunzip_batch_mib=int(rng.choice([0, 1])), **geo)
+                assert p.gunzip(g, out_cap=len(data)) == data, ("gunzip", c, len(data), geo)
             co = zlib.compressobj(6, zlib.DEFLATED, -15)
             ref = len(co.compress(data) + co.flush())
             if len(data) > 100_000:
