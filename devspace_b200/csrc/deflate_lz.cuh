@@ -153,12 +153,15 @@ struct LzParams {
   uint32_t *tok_scratch;      // gridDim.x * kTokSlotWords
   unsigned long long *prof;   // optional: cycles per phase, summed over CTAs (thread 0's clock64 deltas)
   uint32_t no_bulk;           // tuning knob: stage the tiles with plain loads instead of cp.async.bulk
+  uint32_t depth, deep_depth, refine_rounds;  // search effort (kDepth, kDeepDepth, kRefineRounds unless the tools say otherwise)
 };
 
 enum { kProfLoad = 0, kProfInsert, kProfSearch, kProfParse, kProfEmit, kProfHuff, kProfSizes, kProfPack, kProfRefParse,
-       kProfRefList, kProfRefDeep, kProfWaitA, kProfWaitB, kProfJoin, kProfCount,
+       kProfRefList, kProfRefDeep, kProfWaitA, kProfWaitB, kProfJoin, kProfLink, kProfFlat, kProfCount,
        // not phases: sum over warps of (own finish - phase start) / 32, to tell the tail of a phase from its bulk
-       kProfWarpSearch = kProfCount, kProfWarpDeep, kProfSlots };
+       kProfWarpSearch = kProfCount, kProfWarpDeep,
+       // not phases: deep-searched positions and the match bytes they gained
+       kProfDeepItems, kProfDeepGain, kProfSlots };
 
 // named barriers: 0 = the CTA
 enum { kBarTeam = 1 /* +team */, kBarEnd = kBarTeam + kTeams };
@@ -568,19 +571,24 @@ DSG_D void bulk_load_ring(uint8_t *s_data, const LzParams &P, int64_t cs, int rp
 #endif
 }
 
-// Inserts positions [rp0, rp1) into the hash chains in EXACT stream order (nearest candidate first), 1024
-// positions per round, one per thread. Inside a round the threads race, so a thread does a lock-free sorted
-// insertion: it walks past entries of its own round that lie LATER in the stream (they can only be ahead by
-// < 1024 positions) and links itself below them with a compare-and-swap on the link it came through (32-bit
-// CAS on the head table, 16-bit CAS on a prev[] entry). Exact order matters: chains that are only ordered per
-// round cost 1-3 % of compressed size (tools/lzmodel.cc, SCRAMBLE=512).
+// Inserts positions [rp0, rp1) into the hash chains in EXACT stream order (nearest candidate first). Exact order
+// matters: chains that are only ordered per round cost 1-3 % of compressed size (tools/lzmodel.cc, SCRAMBLE=512).
+// Two steps per batch of positions:
+//   pre-hash  all threads of the group, in parallel: the bucket of every position (or "not inserted") into `hpre`;
+//   link      ONE warp, 32 consecutive positions per step: MATCH.ANY groups the lanes of a bucket, a lane links to
+//             the nearest lower lane of its group (same step: the intervening positions are in other buckets) or,
+//             if it is the first of its group, to the bucket's head; the last lane of a group becomes the head.
+//             No compare-and-swap, no retries, no barrier between steps (a warp's shared-memory accesses are
+//             performed in program order; __syncwarp orders them between lanes).
+// The link step is the one strictly ordered step of the tile pipeline (tile t after tile t-1), so its LATENCY
+// bounds the pipeline: 64 short steps per tile instead of 8 rounds of racing sorted insertions (a CAS loop per
+// position with a barrier per round, profiles/r02_lz_phases.md: 33 k cycles per tile, and the teams queued for it).
 // Positions in the interior of a byte run (the five bytes p-1..p+3 are equal) are not inserted: every one of
-// them would land in the same bucket (quadratic walks, useless candidates); the search gives them the
-// distance-1 candidate directly. Their chain start is the start of their run (second pass of insert_positions):
-// a value that does not depend on how the threads interleave, like everything else here -- the output of the kernel
-// is the same on every run (tools/determinism.py).
-constexpr int kInsRound = kLzThreads;
-constexpr int kInsWalkMax = 96;
+// them would land in the same bucket (useless candidates); the search gives them the distance-1 candidate
+// directly. Their chain start is the start of their run (second pass of insert_positions). Nothing here depends
+// on how the threads interleave -- the output of the kernel is the same on every run (tools/determinism.py).
+constexpr int kInsRound = kLzThreads;  // slots this close to a lap behind the current position count as gone (head_entry)
+constexpr uint32_t kNoInsert = 0xffffu;
 
 // interior of a byte run: the five bytes p-1..p+3 are equal
 DSG_D bool run_interior(const uint8_t *s_data, uint32_t slot, uint32_t v, int rp, int lo_rp) {
@@ -589,96 +597,227 @@ DSG_D bool run_interior(const uint8_t *s_data, uint32_t slot, uint32_t v, int rp
 
 // A head word holds the slot of the newest position of its bucket in the low half and that position's ring lap in
 // the high half. The lap tells a live entry from one that is a whole lap (or more) old: its slot belongs to a newer
-// position by now, and following it would walk another bucket's chain or a link that is being written at this
-// moment -- a result that depends on timing. Entries in the last kInsRound positions of the lap window are treated
-// as gone too (their slots alias the positions of the running round); they lie beyond kMaxDist anyway.
+// position by now, and following it would walk another bucket's chain. Entries in the last kInsRound positions of
+// the lap window are treated as gone too; they lie beyond kMaxDist anyway.
 DSG_D uint32_t head_word(int rp) { return ring_slot(rp) | ((uint32_t)((rp + kDict) / kRing) << 16); }
 
 // Slot of the entry a head word names, or kNil when the entry is not live as seen from position rp.
-// ahead_ok: positions later in the stream (by less than kInsRound) count as live.
-DSG_D uint32_t head_entry(uint32_t word, int rp, bool ahead_ok) {
+DSG_D uint32_t head_entry(uint32_t word, int rp) {
   const uint32_t s = word & 0xffffu;
   if (s == kNil) return kNil;
   const int cur = rp + kDict;                                   // ring position index of rp
   const int ent = (int)(word >> 16) * kRing + (int)s;           // ... of the entry
   const int delta = cur - ent;                                  // > 0: the entry is older
-  if (delta >= kRing - kInsRound || delta <= (ahead_ok ? -kInsRound : 0)) return kNil;
+  if (delta >= kRing - kInsRound || delta <= 0) return kNil;
   return s;
 }
 
-DSG_D void insert_one(const uint8_t *s_data, unsigned short *prev16, uint32_t *s_head, int rp, int lo_rp) {
-  const uint32_t slot = ring_slot(rp);
-  const uint32_t v = load4(s_data + slot);
-  const uint32_t h = hash4(v);
-  if (run_interior(s_data, slot, v, rp, lo_rp)) return;  // gets its chain start in the second pass
-  const uint32_t mine = head_word(rp);
-  bool at_head = true;
-  uint32_t holder = h;  // the link we would be written into: head[h], or prev[holder]
-  int walked = 0;
-  for (;;) {
-    const uint32_t word = at_head ? s_head[holder] : (uint32_t)prev16[holder];
-    const uint32_t nxt = at_head ? head_entry(word, rp, true) : word;
-    // The bound guards against an unexpectedly long stretch of entries of this round in one bucket.
-    if (nxt != kNil && ++walked < kInsWalkMax) {
-      int fwd = (int)nxt - (int)slot;
-      if (fwd < 0) fwd += kRing;
-      if (fwd > 0 && fwd < kInsRound) {  // an entry of this round that is later in the stream
-        at_head = false;
-        holder = nxt;
-        continue;
+// What a thread keeps between the two parts of an insertion.
+struct InsPrep {
+  uint32_t list_start, list_count;  // the class list of this thread's WARP inside l_pos / l_hv (uniform in the warp)
+  uint32_t lead;                    // run interiors at the start of this thread's positions whose run starts before
+                                    // the range: their chain start is the carried run start (ordered part)
+  uint32_t last;                    // range index + 1 of the last position of the range that is not an interior, 0 = none
+};
+
+constexpr int kInsClasses = kTeamWarps;  // bucket classes = warps of a team
+static_assert(kInsClasses == 8 && kRun == 8 && kTile <= 65535, "packed class counters: 2 x 4 fields of 16 bits");
+
+// Part one, NOT ordered (needs only the bytes of the range): buckets of positions [rp0, rp0 + n), n <= kTile, eight
+// consecutive positions per thread; a stable partition of the inserted positions by bucket class (bucket & 7) into
+// l_pos (range index) / l_hv (bucket) -- class c occupies one contiguous stretch, in stream order; chain starts of
+// the run interiors whose run starts inside the range. `scratch`: 40 words, 8-byte aligned. Two team barriers inside.
+DSG_D InsPrep insert_prepare(const uint8_t *s_data, unsigned short *prev16, uint16_t *l_pos, uint16_t *l_hv,
+                             uint32_t *scratch, int rp0, int n, int lo_rp, const LzGroup &g) {
+  const uint32_t lane = (uint32_t)g.tid & 31u, w = (uint32_t)g.tid >> 5;
+  const int i0 = g.tid * kRun;
+  uint32_t hv[kRun];
+  uint64_t ca = 0, cb = 0;  // positions per class: classes 0-3 and 4-7, 16 bits each
+  uint32_t last = 0;
+  const uint32_t slot0 = ring_slot(rp0 + i0);
+  if (i0 < n) {
+    // the thread's 8 + 3 bytes from four aligned words (reads run on into the mirror behind the ring end), the byte
+    // before them on its own
+    const uint32_t m8 = 8u * (slot0 & 3u);
+    const uint32_t *wp = reinterpret_cast<const uint32_t *>(s_data + (slot0 & ~3u));
+    const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2], w3 = wp[3];
+    const uint32_t x0 = __funnelshift_r(w0, w1, m8), x1 = __funnelshift_r(w1, w2, m8), x2 = __funnelshift_r(w2, w3, m8);
+    uint32_t before = s_data[slot0 ? slot0 - 1 : kRing - 1];
+#pragma unroll
+    for (int j = 0; j < kRun; j++) {
+      const int i = i0 + j;
+      const uint32_t v = j < 4 ? __funnelshift_r(x0, x1, 8 * (j & 3)) : __funnelshift_r(x1, x2, 8 * (j & 3));
+      // interior of a byte run (run_interior): the five bytes p-1..p+3 are equal
+      const bool interior = rp0 + i > lo_rp && v == (v & 0xffu) * 0x01010101u && before == (v & 0xffu);
+      before = v & 0xffu;
+      hv[j] = kNoInsert;
+      if (i < n && !interior) {
+        hv[j] = hash4(v);
+        last = (uint32_t)i + 1u;
+        const uint64_t one = 1ull << (16 * (hv[j] & 3u));
+        if (hv[j] & 4u) cb += one;
+        else ca += one;
       }
     }
-    // Our own link is written before we become reachable: both are shared-memory operations of this thread
-    // and the shared-memory pipeline of an SM performs a warp's accesses in program order.
-    prev16[slot] = (unsigned short)nxt;
-#if defined(DSG_EMU)
-    __threadfence_block();
-#else
-    asm volatile("" ::: "memory");
-#endif
-    const uint32_t seen = at_head ? atomicCAS(&s_head[holder], word, mine)
-                                  : (uint32_t)atomicCAS(&prev16[holder], (unsigned short)word, (unsigned short)slot);
-    if (seen == word) break;  // else somebody linked in first: look at the same link again
+  } else {
+#pragma unroll
+    for (int j = 0; j < kRun; j++) hv[j] = kNoInsert;
   }
-}
-
-// `run_start` (shared memory, one word per run of chunks): position + kDict + 1 of the last position before rp0 that
-// is not a run interior, 0 = none; updated to the same for rp1. `scratch`: >= 33 words for the scan.
-DSG_D void insert_positions(const uint8_t *s_data, uint16_t *s_prev, uint32_t *s_head, int rp0, int rp1, int lo_rp,
-                            const LzGroup &g, uint32_t *scratch, uint32_t *run_start) {
-  unsigned short *prev16 = reinterpret_cast<unsigned short *>(s_prev);
-  for (int base = rp0; base < rp1; base += g.n) {  // g.n <= kInsRound positions per round (two per thread: slower)
-    const int r0 = base + g.tid;
-    if (r0 < rp1) insert_one(s_data, prev16, s_head, r0, lo_rp);
-    group_sync(g);  // rounds are ordered
-  }
-  // Second pass: every run interior gets the START of its byte run as its chain start -- the nearest position before
-  // it that is not an interior; that position sits in the same bucket (its four bytes are the run byte too), so its
-  // own link leads on to the earlier runs. A running maximum over the range, carried from range to range.
-  const int per = (rp1 - rp0 + g.n - 1) / g.n;
-  const int lo = rp0 + g.tid * per < rp1 ? rp0 + g.tid * per : rp1;
-  const int hi = lo + per < rp1 ? lo + per : rp1;
-  uint32_t last = 0;
-  for (int r = lo; r < hi; r++) {
-    const uint32_t slot = ring_slot(r);
-    if (!run_interior(s_data, slot, load4(s_data + slot), r, lo_rp)) last = (uint32_t)(r + kDict + 1);
-  }
-  uint32_t total;
-  uint32_t cur = group_exclusive_max(last, scratch, &total, g);
-  const uint32_t carry = *run_start;
-  if (cur == 0) cur = carry;
-  for (int r = lo; r < hi; r++) {
-    const uint32_t slot = ring_slot(r);
-    if (run_interior(s_data, slot, load4(s_data + slot), r, lo_rp)) {
-      const int start_rp = (int)cur - kDict - 1;
-      prev16[slot] = (cur != 0 && r - start_rp <= kMaxDist) ? (unsigned short)ring_slot(start_rp) : (unsigned short)kNil;
-    } else {
-      cur = (uint32_t)(r + kDict + 1);
+  // inclusive scan inside the warp: class counts (sum) and the last non-interior position (max)
+  uint64_t sa = ca, sb = cb;
+  uint32_t sl = last;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint64_t ta = __shfl_up_sync(0xffffffffu, sa, o), tb = __shfl_up_sync(0xffffffffu, sb, o);
+    const uint32_t tl = __shfl_up_sync(0xffffffffu, sl, o);
+    if (lane >= (uint32_t)o) {
+      sa += ta;
+      sb += tb;
+      sl = sl > tl ? sl : tl;
     }
   }
-  group_sync(g);  // everybody has read the carry
-  if (g.tid == 0 && total != 0) *run_start = total;
+  uint32_t el = __shfl_up_sync(0xffffffffu, sl, 1);  // exclusive: the threads before this one
+  if (lane == 0) el = 0;
+  uint64_t *scr64 = reinterpret_cast<uint64_t *>(scratch);
+  group_sync(g);  // the scratch is free (previous use)
+  if (lane == 31) {
+    scr64[2 * w] = sa;
+    scr64[2 * w + 1] = sb;
+    scratch[32 + w] = sl;
+  }
   group_sync(g);
+  uint64_t ta = 0, tb = 0, pa = 0, pb = 0;
+  uint32_t tl = 0, pl = 0;
+#pragma unroll
+  for (uint32_t k = 0; k < (uint32_t)kInsClasses; k++) {
+    const uint64_t xa = scr64[2 * k], xb = scr64[2 * k + 1];
+    const uint32_t xl = scratch[32 + k];
+    if (k < w) {
+      pa += xa;
+      pb += xb;
+      pl = pl > xl ? pl : xl;
+    }
+    ta += xa;
+    tb += xb;
+    tl = tl > xl ? tl : xl;
+  }
+  if (pl > el) el = pl;
+  // class stretches: exclusive prefix over the eight class totals (a multiplication sums the 16-bit fields below)
+  const uint64_t kOnes = 0x0001000100010001ull;
+  const uint64_t ia = ta * kOnes, ib = tb * kOnes;      // inclusive inside each half
+  const uint64_t ea = ia << 16, eb = (ib << 16) + (ia >> 48) * kOnes;
+  uint64_t oa = ea + pa + (sa - ca), ob = eb + pb + (sb - cb);  // where this thread's positions of every class go
+#pragma unroll
+  for (int j = 0; j < kRun; j++) {
+    if (hv[j] != kNoInsert) {
+      const uint32_t sh = 16 * (hv[j] & 3u);
+      uint32_t at;
+      if (hv[j] & 4u) {
+        at = (uint32_t)(ob >> sh) & 0xffffu;
+        ob += 1ull << sh;
+      } else {
+        at = (uint32_t)(oa >> sh) & 0xffffu;
+        oa += 1ull << sh;
+      }
+      l_pos[at] = (uint16_t)(i0 + j);
+      l_hv[at] = (uint16_t)hv[j];
+    }
+  }
+  // Run interiors get the START of their byte run as their chain start -- the nearest position before them that is
+  // not an interior; that position sits in the same bucket (its four bytes are the run byte too), so its own link
+  // leads on to the earlier runs.
+  InsPrep r;
+  r.lead = 0;
+  uint32_t cur = el;
+#pragma unroll
+  for (int j = 0; j < kRun; j++) {
+    const int i = i0 + j;
+    if (i < n) {
+      if (hv[j] != kNoInsert) {
+        cur = (uint32_t)i + 1u;
+      } else if (cur == 0) {
+        r.lead++;
+      } else {
+        const int dist = i - ((int)cur - 1);
+        const uint32_t sl = slot0 + (uint32_t)j;
+        prev16[sl < (uint32_t)kRing ? sl : sl - (uint32_t)kRing] =
+            dist <= kMaxDist ? (unsigned short)ring_slot(rp0 + (int)cur - 1) : (unsigned short)kNil;
+      }
+    }
+  }
+  const uint32_t sh = 16 * (w & 3u);
+  r.list_start = (uint32_t)(((w & 4u) ? eb : ea) >> sh) & 0xffffu;
+  r.list_count = (uint32_t)(((w & 4u) ? tb : ta) >> sh) & 0xffffu;
+  r.last = tl;
+  return r;
+}
+
+// Part two, ORDERED (range after range along the stream): every warp links the positions of its bucket class, 32
+// per step, in stream order; the classes are disjoint sets of buckets, so the warps do not meet. In a step every
+// lane reads the head of its bucket, then writes itself there and reads the head back: a lane that finds itself is
+// alone in its bucket (the common case: 32 positions, 1024 buckets per class) and links to the old head. Lanes that
+// share a bucket find each other with a second write (now the first winner sees a foreign word too) and a MATCH.ANY
+// in which all the other lanes pass one common value -- the instruction costs ~12 cycles per DISTINCT value and
+// runs one warp at a time per SM (tools/micro_match.cu: 377 cycles for 32 distinct buckets, 512 with eight warps
+// at it, 18 for four values): a lane of a shared bucket links to the nearest lower lane of its group (the positions between
+// them are in other buckets), the first of a group to the old head, and the last lane of a group becomes the head.
+// `run_start` (shared memory, one word per run of chunks): position + kDict + 1 of the last position before rp0 that
+// is not a run interior, 0 = none; updated to the same for the end of the range. Ends with a team barrier.
+DSG_D void insert_link(unsigned short *prev16, uint32_t *s_head, const uint16_t *l_pos, const uint16_t *l_hv,
+                       const InsPrep &prep, int rp0, const LzGroup &g, uint32_t *run_start) {
+  const uint32_t lane = (uint32_t)g.tid & 31u;
+  uint32_t pos_n = 0, hv_n = 0;  // the next step's entry, fetched a step ahead
+  if (lane < prep.list_count) {
+    pos_n = l_pos[prep.list_start + lane];
+    hv_n = l_hv[prep.list_start + lane];
+  }
+  for (uint32_t k0 = 0; k0 < prep.list_count; k0 += 32) {
+    const bool active = k0 + lane < prep.list_count;
+    const uint32_t pos = pos_n, hv = hv_n;
+    if (k0 + 32 + lane < prep.list_count) {
+      pos_n = l_pos[prep.list_start + k0 + 32 + lane];
+      hv_n = l_hv[prep.list_start + k0 + 32 + lane];
+    }
+    const int rp = rp0 + (int)pos;
+    const uint32_t mine = head_word(rp);
+    const uint32_t old = active ? s_head[hv] : 0u;
+    __syncwarp();  // the old heads are read before any lane of this step replaces one
+    if (active) s_head[hv] = mine;
+    __syncwarp();
+    const bool lost = active && s_head[hv] != mine;
+    uint32_t link = old;      // what this position links to: a head word ...
+    bool link_is_word = true;  // ... or the range index of a position of this step
+    if (__any_sync(0xffffffffu, lost)) {
+      __syncwarp();
+      if (lost) s_head[hv] = mine;  // the first winner of a shared bucket now reads a foreign word as well
+      __syncwarp();
+      const bool shared = active && (lost || s_head[hv] != mine);
+      __syncwarp();
+      // all lanes take part; the lanes that are alone in their bucket pass ONE common value (cost per distinct value)
+      const uint32_t grp = __match_any_sync(0xffffffffu, shared ? hv : 0xffffffffu);
+      const uint32_t lower = shared ? grp & ((1u << lane) - 1u) : 0u;
+      const uint32_t below = __shfl_sync(0xffffffffu, pos, lower ? 31 - __clz((int)lower) : (int)lane);
+      if (lower) {
+        link = below;
+        link_is_word = false;
+      }
+      if (shared && (grp >> lane) == 1u) s_head[hv] = mine;  // the last position of the bucket in this step
+    }
+    if (active)
+      prev16[ring_slot(rp)] = (unsigned short)(link_is_word ? head_entry(link, rp) : ring_slot(rp0 + (int)link));
+    __syncwarp();  // the heads are written before the next step reads them
+  }
+  if (prep.lead) {
+    const uint32_t carry = *run_start;
+    const int start_rp = (int)carry - kDict - 1;
+    const unsigned short start_slot = carry ? (unsigned short)ring_slot(start_rp) : (unsigned short)kNil;
+    for (uint32_t j = 0; j < prep.lead; j++) {
+      const int r = rp0 + g.tid * kRun + (int)j;
+      prev16[ring_slot(r)] = (carry && r - start_rp <= kMaxDist) ? start_slot : (unsigned short)kNil;
+    }
+  }
+  group_sync(g);  // everybody has read the carry; the range is in the chains
+  if (g.tid == 0 && prep.last) *run_start = (uint32_t)(rp0 + (int)prep.last - 1 + kDict + 1);
 }
 
 // Longest match for every position of the tile. tile_rp = run-relative position of the tile start, chunk_end =
@@ -719,7 +858,7 @@ DSG_D void search_way_init(SearchWay &w, const uint8_t *s_data, int tile_rp, int
 
 // Sets up position w.j of the run (inheritance, window, chain start, byte-run candidate).
 DSG_D void search_way_setup(SearchWay &w, const uint8_t *s_data, const uint16_t *s_prev, int tile_rp, int chunk_end,
-                            int lo_rp) {
+                            int lo_rp, int depth_cfg) {
   enum { kWalk = 1, kCmp = 2 };
   const int rp = tile_rp + w.pos0 + w.j;
   w.maxlen = chunk_end - rp < kMaxMatch ? chunk_end - rp : kMaxMatch;
@@ -737,7 +876,7 @@ DSG_D void search_way_setup(SearchWay &w, const uint8_t *s_data, const uint16_t 
       w.bdist = w.inh_dist;
     }
     w.max_back = rp - lo_rp < kMaxDist ? rp - lo_rp : kMaxDist;
-    w.depth = w.best >= kNice ? 0 : (w.best >= kGood ? kDepth / 4 : kDepth);
+    w.depth = w.best >= kNice ? 0 : (w.best >= kGood ? depth_cfg / 4 : depth_cfg);
     w.q = s_prev[w.slot];
     w.aw = w.a[w.best];  // the byte a longer match has to reproduce (cheap first filter)
     const bool in_run = v == w.v_prev && w.max_back > 0;  // interior of a byte run
@@ -813,7 +952,7 @@ DSG_D void search_walk_step(SearchWay &w, const uint8_t *s_data, const uint16_t 
 
 // Chain exhausted: record the position and set up the next one of the run (the caller hands out a new run).
 DSG_D void search_finish_position(SearchWay &w, const uint8_t *s_data, const uint16_t *s_prev, uint8_t *s_mlen,
-                                  uint16_t *s_mdist, int tile_rp, int chunk_end, int lo_rp) {
+                                  uint16_t *s_mdist, int tile_rp, int chunk_end, int lo_rp, int depth_cfg) {
   if (w.best < kMinMatch) w.best = 0;
   s_mlen[w.pos0 + w.j] = (uint8_t)(w.best ? w.best - 3 : 0);  // 0 = no match, else len-3 in 1..255
   // bit 15: the walk stopped at the depth limit with the chain unfinished -> worth a deep second look
@@ -828,7 +967,7 @@ DSG_D void search_finish_position(SearchWay &w, const uint8_t *s_data, const uin
     w.slot = 0;
     w.a = s_data;
   }
-  if (w.j < kSearchRun) search_way_setup(w, s_data, s_prev, tile_rp, chunk_end, lo_rp);
+  if (w.j < kSearchRun) search_way_setup(w, s_data, s_prev, tile_rp, chunk_end, lo_rp, depth_cfg);
 }
 
 // Positions are handed out in runs of kSearchRun through a shared-memory counter: a lane that finishes its run
@@ -839,26 +978,26 @@ DSG_D void search_finish_position(SearchWay &w, const uint8_t *s_data, const uin
 // thread, two interleaved runs per thread, and warp-voted scheduling of the three actions.
 // `ctr` must be zero on entry.
 DSG_D void search_tile(const uint8_t *s_data, const uint16_t *s_prev, uint8_t *s_mlen, uint16_t *s_mdist, int tile_rp,
-                       int tile_len, int chunk_end, int lo_rp, uint32_t *ctr) {
+                       int tile_len, int chunk_end, int lo_rp, uint32_t *ctr, int depth_cfg) {
   enum { kWalk = 1, kCmp = 2 };
   const uint32_t nruns = (uint32_t)((tile_len + kSearchRun - 1) / kSearchRun);
   SearchWay w;
   uint32_t run = atomicAdd(ctr, 1u);
   if (run >= nruns) return;
   search_way_init(w, s_data, tile_rp, (int)run * kSearchRun, lo_rp);
-  search_way_setup(w, s_data, s_prev, tile_rp, chunk_end, lo_rp);
+  search_way_setup(w, s_data, s_prev, tile_rp, chunk_end, lo_rp, depth_cfg);
   for (;;) {
     if (w.st == kCmp) {
       search_cmp_step(w);
     } else if (w.depth > 0 && w.q != kNil) {
       search_walk_step(w, s_data, s_prev);
     } else {
-      search_finish_position(w, s_data, s_prev, s_mlen, s_mdist, tile_rp, chunk_end, lo_rp);
+      search_finish_position(w, s_data, s_prev, s_mlen, s_mdist, tile_rp, chunk_end, lo_rp, depth_cfg);
       if (w.j >= kSearchRun) {
         run = atomicAdd(ctr, 1u);
         if (run >= nruns) break;
         search_way_init(w, s_data, tile_rp, (int)run * kSearchRun, lo_rp);
-              search_way_setup(w, s_data, s_prev, tile_rp, chunk_end, lo_rp);
+        search_way_setup(w, s_data, s_prev, tile_rp, chunk_end, lo_rp, depth_cfg);
       }
     }
   }
@@ -927,13 +1066,23 @@ DSG_D uint32_t refine_build_list(const uint8_t *s_mlen, const uint16_t *s_mdist,
 // Speculative links past the end of a chain are kNil or stale slots: both are valid shared-memory indices.
 constexpr int kChase = 4;
 
-DSG_D void refine_search(const uint8_t *s_data, const uint16_t *s_prev, uint8_t *s_mlen, uint16_t *s_mdist,
-                         const uint16_t *s_work, uint32_t nwork, int tile_rp, int tile_len, int chunk_end, int lo_rp,
-                         uint32_t *ctr) {
+// `pass`: kPassAll = every listed position; kPassSample = every eighth one (the gate of the refine rounds measures
+// what the deep search gains on them); kPassRest = the others. `ctr_base` = value of the counter at entry (a pass
+// leaves it at its item count + one failed take per thread). Returns the match bytes this thread's positions gained.
+enum { kPassAll = 0, kPassSample, kPassRest };
+constexpr uint32_t kSampleStride = 8;
+
+DSG_D uint32_t refine_search(const uint8_t *s_data, const uint16_t *s_prev, uint8_t *s_mlen, uint16_t *s_mdist,
+                             const uint16_t *s_work, uint32_t nwork, int tile_rp, int tile_len, int chunk_end, int lo_rp,
+                             uint32_t *ctr, uint32_t ctr_base, int deep_cfg, int pass) {
   const SmemBase sd = smem_base(s_data), sp = smem_base(s_prev);
+  const uint32_t nsample = (nwork + kSampleStride - 1) / kSampleStride;
+  const uint32_t nitems = pass == kPassSample ? nsample : (pass == kPassRest ? nwork - nsample : nwork);
+  uint32_t gain = 0;
   for (;;) {
-    const uint32_t k = atomicAdd(ctr, 1u);
-    if (k >= nwork) break;
+    const uint32_t j = atomicAdd(ctr, 1u) - ctr_base;
+    if (j >= nitems) break;
+    const uint32_t k = pass == kPassSample ? kSampleStride * j : (pass == kPassRest ? j + j / (kSampleStride - 1) + 1 : j);
     const uint32_t item = s_work[k];
     const int tp = (int)(item & 0x7fffu);
     const int rp = tile_rp + tp;
@@ -942,10 +1091,11 @@ DSG_D void refine_search(const uint8_t *s_data, const uint16_t *s_prev, uint8_t 
     const int maxlen = chunk_end - rp < kMaxMatch ? chunk_end - rp : kMaxMatch;
     const uint32_t cur = s_mlen[tp];
     int best = cur ? (int)cur + 3 : 0;
+    const int best0 = best;
     int bdist = cur ? (int)(s_mdist[tp] & 0x7fff) : 0;
     if (maxlen < kMinMatch || best >= kNice || best >= maxlen) continue;
     const int max_back = rp - lo_rp < kMaxDist ? rp - lo_rp : kMaxDist;
-    int depth = (item & 0x8000u) ? kDeepDepth / 4 : kDeepDepth;  // see refine_build_list
+    int depth = (item & 0x8000u) ? deep_cfg / 4 : deep_cfg;  // see refine_build_list
     int cmps = kMaxCompares;
     int last_d = 0;
     uint32_t q = s_prev[slot];
@@ -1013,8 +1163,10 @@ DSG_D void refine_search(const uint8_t *s_data, const uint16_t *s_prev, uint8_t 
     if (best >= kMinMatch) {
       s_mlen[tp] = (uint8_t)(best - 3);
       s_mdist[tp] = (uint16_t)bdist;
+      gain += (uint32_t)(best - best0);
     }
   }
+  return gain;
 }
 
 // next(p) for the stateless lazy parse; tp is tile-relative, tile_len = positions of this tile inside the chunk
@@ -1280,6 +1432,7 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
   uint32_t *t_deep = s_deep + team * (kTile / 32);
   uint32_t *t_scan = s_misc + kMTeamScan + team * kMTeamScanStride;
   uint32_t *t_ctr = s_misc + kMRunCtr + team;
+  unsigned short *prev16 = reinterpret_cast<unsigned short *>(s_prev);
 
   // one mbarrier per team for the bulk staging of its tiles (8-byte words behind the scan scratch of s_misc)
   uint32_t bulk_phase = 0;  // parity of the team's next mbarrier phase (uniform inside the team)
@@ -1353,7 +1506,18 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
         s_misc[kMStale] = 0;
       }
       __syncthreads();
-      insert_positions(s_data, s_prev, s_head, lo_rp, crp, lo_rp, g_all, s_misc + kMScan, &s_misc[kMRunStart]);
+      // the window goes into the chains like tiles do: every team prepares a stretch of kTile positions, then the
+      // teams link their stretches one after the other
+      for (int base = lo_rp; base < crp; base += kTeams * kTile) {
+        const int b0 = base + (int)team * kTile;
+        const int nb = crp - b0 < 0 ? 0 : (crp - b0 < kTile ? crp - b0 : kTile);
+        const InsPrep prep = insert_prepare(s_data, prev16, t_work, t_mdist, t_bitmap, b0, nb, lo_rp, g_team);
+        for (uint32_t j = 0; j < (uint32_t)kTeams; j++) {
+          __syncthreads();
+          if (team == j && nb > 0) insert_link(prev16, s_head, t_work, t_mdist, prep, b0, g_team, &s_misc[kMRunStart]);
+        }
+      }
+      __syncthreads();
       LZ_PROF(kProfLoad);
     }
     for (uint32_t i = tid; i < 288; i += kLzThreads) s_lfreq[i] = 0;
@@ -1366,6 +1530,7 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
     }
     chunk_flatness(P.in, P.len, cs, chunk_len, reinterpret_cast<uint32_t *>(s_work), &s_misc[kMFlat]);  // barriers inside
     __syncthreads();
+    LZ_PROF(kProfFlat);
 
     // ---- tiles: a pipeline over four teams ---------------------------------------------------------------------
     // A team (8 warps) runs, for the tile it holds, stage A (load, hash, shallow search), stage B (parse / deep search
@@ -1394,35 +1559,39 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
       // copy does not have to wait for the hashing of tile t-1 and overlaps that wait. (The first tile of a window came
       // with the dictionary; it is loaded again, the same bytes.)
       const bool staged = tile_rp > 0;
-      const bool bulk = staged && bulk_ok(P, rs, tile_rp + kLook, tile_rp + kTile + kLook);
+      // 16 bytes more at the front (the byte before the tile decides whether its first position is a run interior)
+      // and the first kLook bytes, which the tile before this one has loaded or is loading as its look-ahead -- the
+      // same bytes to the same slots: with them the team can prepare the insertion without waiting for that tile.
+      const int load_lo = tile_rp - 16, load_hi = tile_rp + kTile + kLook;
+      const bool bulk = staged && bulk_ok(P, rs, load_lo, load_hi);
       if (bulk) {
-        if (g_team.tid == 0) bulk_load_ring(s_data, P, rs, tile_rp + kLook, tile_rp + kTile + kLook, t_mbar);
+        if (g_team.tid == 0) bulk_load_ring(s_data, P, rs, load_lo, load_hi, t_mbar);
       } else if (staged) {
-        load_ring(s_data, P, rs, tile_rp + kLook, tile_rp + kTile + kLook, g_team);
+        load_ring(s_data, P, rs, load_lo, load_hi, g_team);
       }
-      LZ_PROF(kProfLoad);
       const uint32_t seq = seq_base + (uint32_t)t;  // t > 0: seq - 1 is the previous tile of this chunk
       // One warp of the team does the waiting (a waiting warp re-issues its try_wait; eight of them take issue slots
       // from the teams that are working), the others park at the team's barrier.
-      if (g_team.tid < 32) {
-        if (t > 0) sig_wait(s_sig, kSigIns + (int)((seq - 1) & (kSigRing - 1)), (seq - 1) / kSigRing);  // tile t-1 is in the chains
 #if !defined(DSG_EMU)
-        if (bulk) mbar_wait(t_mbar, bulk_phase);
+      if (bulk && g_team.tid < 32) mbar_wait(t_mbar, bulk_phase);
 #endif
-      }
-      LZ_PROF(kProfWaitA);
       if (bulk) bulk_phase ^= 1u;
-      if (staged || t > 0) group_sync(g_team);
+      if (staged) group_sync(g_team);
       LZ_PROF(kProfLoad);
-      insert_positions(s_data, s_prev, s_head, tile_rp, tile_rp + tile_len, lo_rp, g_team, t_scan,
-                       &s_misc[kMRunStart]);  // ends with a barrier
-      if (g_team.tid == 0) sig_arrive(s_sig, kSigIns + (int)(seq & (kSigRing - 1)));  // (behind the team barrier)
+      const InsPrep prep = insert_prepare(s_data, prev16, t_work, t_mdist, t_bitmap, tile_rp, tile_len, lo_rp, g_team);
       LZ_PROF(kProfInsert);
+      // tile t-1 is in the chains
+      if (t > 0 && g_team.tid < 32) sig_wait(s_sig, kSigIns + (int)((seq - 1) & (kSigRing - 1)), (seq - 1) / kSigRing);
+      group_sync(g_team);  // ... and the team's class lists are complete
+      LZ_PROF(kProfWaitA);
+      insert_link(prev16, s_head, t_work, t_mdist, prep, tile_rp, g_team, &s_misc[kMRunStart]);  // ends with a barrier
+      if (g_team.tid == 0) sig_arrive(s_sig, kSigIns + (int)(seq & (kSigRing - 1)));  // (behind the team barrier)
+      LZ_PROF(kProfLink);
       if (g_team.tid == 0) *t_ctr = 0;
       for (uint32_t i = (uint32_t)g_team.tid; i < (uint32_t)kTile / 32; i += kTeamThreads) t_deep[i] = 0;
       group_sync(g_team);
       const long long t_ws = P.prof ? clock64() : 0;
-      search_tile(s_data, s_prev, t_mlen, t_mdist, tile_rp, tile_len, crp + chunk_len, lo_rp, t_ctr);
+      search_tile(s_data, s_prev, t_mlen, t_mdist, tile_rp, tile_len, crp + chunk_len, lo_rp, t_ctr, (int)P.depth);
       if (P.prof && team == 0 && lane == 0)
         atomicAdd(&P.prof[kProfWarpSearch], (unsigned long long)(clock64() - t_ws) / kTeamWarps);
       group_sync(g_team);
@@ -1447,7 +1616,7 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
       // -- stage B: the refine rounds parse from the tile start (the true first token start is not known before tile
       // t-1 has been parsed for good; a parse from a wrong start joins the true one within a few tokens, and this
       // way the choice of deep-searched positions does not depend on timing)
-      for (int r = 0; r < kRefineRounds; r++) {
+      for (int r = 0; r < (int)P.refine_rounds; r++) {
         parse_tile_wide(t_mlen, t_bitmap, 0, tile_len, g_team);
         if (g_team.tid == 0) *t_ctr = 0;
         group_sync(g_team);
@@ -1457,7 +1626,13 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
         if (nwork == 0) break;  // nothing to look at more deeply (random, zero and record pages): a further round would
                                 // parse the same lengths again and find the same empty list (uniform: nwork is a scan total)
         const long long t_wd = P.prof ? clock64() : 0;
-        refine_search(s_data, s_prev, t_mlen, t_mdist, t_work, nwork, tile_rp, tile_len, crp + chunk_len, lo_rp, t_ctr);
+        uint32_t gain = refine_search(s_data, s_prev, t_mlen, t_mdist, t_work, nwork, tile_rp, tile_len, crp + chunk_len,
+                                      lo_rp, t_ctr, 0u, (int)P.deep_depth, kPassAll);
+        if (P.prof) {
+          for (int o = 16; o > 0; o >>= 1) gain += __shfl_xor_sync(0xffffffffu, gain, o);
+          if (lane == 0) atomicAdd(&P.prof[kProfDeepGain], (unsigned long long)gain);
+          if (g_team.tid == 0) atomicAdd(&P.prof[kProfDeepItems], (unsigned long long)nwork);
+        }
         if (P.prof && team == 0 && lane == 0)
           atomicAdd(&P.prof[kProfWarpDeep], (unsigned long long)(clock64() - t_wd) / kTeamWarps);
         group_sync(g_team);

@@ -423,6 +423,12 @@ int lz_launch(dsg_ctx *ctx, cudaStream_t stream, const uint8_t *d_in, uint64_t l
   P.tok_scratch = b_tok.as<uint32_t>();
   P.prof = nullptr;
   P.no_bulk = (ctx->opts.lz_flags & DSG_LZ_NO_BULK) ? 1u : 0u;
+  {  // search effort: the defaults, unless a profiling tool passes others in the upper bits of lz_flags
+    const uint32_t f = ctx->opts.lz_flags;
+    P.deep_depth = ((f >> 8) & 0xffu) ? 4u * ((f >> 8) & 0xffu) : (uint32_t)kDeepDepth;
+    P.refine_rounds = ((f >> 16) & 3u) == 0 ? (uint32_t)kRefineRounds : (((f >> 16) & 3u) == 3u ? 0u : ((f >> 16) & 3u));
+    P.depth = ((f >> 18) & 15u) ? ((f >> 18) & 15u) : (uint32_t)kDepth;
+  }
   const bool prof_on = (ctx->opts.lz_flags & DSG_LZ_PROFILE) != 0;  // development aid: per-phase cycle counts on stderr
   if (prof_on) {
     CU(ctx->lz_prof.ensure(sizeof(unsigned long long) * kProfSlots));
@@ -441,13 +447,13 @@ int lz_launch(dsg_ctx *ctx, cudaStream_t stream, const uint8_t *d_in, uint64_t l
     CU(cudaMemcpyAsync(h, P.prof, sizeof h, cudaMemcpyDeviceToHost, stream));
     CU(cudaStreamSynchronize(stream));
     static const char *names[kProfCount] = {"load", "insert", "search", "parse", "emit", "huffman", "sizes", "pack",
-                                              "ref_parse", "ref_list", "ref_deep", "wait_a", "wait_b", "join"};
+                                              "ref_parse", "ref_list", "ref_deep", "wait_a", "wait_b", "join", "link", "flat"};
     unsigned long long tot = 0;
     for (int i = 0; i < kProfCount; i++) tot += h[i];
     fprintf(stderr, "[lz prof] chunks=%u grid=%u cycles/chunk:", nchunks, grid);
     for (int i = 0; i < kProfCount; i++) fprintf(stderr, " %s=%llu", names[i], h[i] / nchunks);
-    fprintf(stderr, " total=%llu (mean warp finish: search=%llu ref_deep=%llu)\n", tot / nchunks,
-            h[kProfWarpSearch] / nchunks, h[kProfWarpDeep] / nchunks);
+    fprintf(stderr, " total=%llu (mean warp finish: search=%llu ref_deep=%llu; deep-searched positions %llu, match bytes gained %llu)\n",
+            tot / nchunks, h[kProfWarpSearch] / nchunks, h[kProfWarpDeep] / nchunks, h[kProfDeepItems], h[kProfDeepGain]);
   }
   return DSG_OK;
 }

@@ -107,10 +107,11 @@ class Packer:
 
     # -- plumbing -------------------------------------------------------------------------------------
     def _opts(self, chunk_units: int = 0, run_chunks: int = 0, grid: int = 0, tail_bytes: Optional[int] = None,
-              profile: bool = False, no_bulk: bool = False, gunzip_batch_mib: int = 0) -> DsgOpts:
+              profile: bool = False, no_bulk: bool = False, gunzip_batch_mib: int = 0, effort: int = 0) -> DsgOpts:
         level, segment_bytes, flags = self._base
+        # effort (profiling tools only): search effort in bits 8.. of lz_flags, see lz_launch in dsgpack.cu; 0 = default
         lz_flags = ((_lib.DSG_LZ_TAIL_SET if tail_bytes is not None else 0) | (_lib.DSG_LZ_PROFILE if profile else 0)
-                    | (_lib.DSG_LZ_NO_BULK if no_bulk else 0))
+                    | (_lib.DSG_LZ_NO_BULK if no_bulk else 0) | ((effort & 0xffffff) << 8))
         return DsgOpts(ctypes.sizeof(DsgOpts), level, segment_bytes, flags, gunzip_batch_mib, chunk_units, run_chunks, grid,
                        lz_flags,
                        int(tail_bytes or 0))

@@ -110,6 +110,9 @@ int emu_lz_deflate(const uint8_t *in, uint64_t len, const uint8_t *dict, uint32_
   P.tok_scratch = tok.data();
   P.prof = nullptr;
   P.no_bulk = 0;
+  P.depth = kDepth;
+  P.deep_depth = kDeepDepth;
+  P.refine_rounds = kRefineRounds;
   emu::launch(dim3(grid), dim3(kLzThreads), LzLayout::total, [&] { lz_deflate_kernel(P); });
   emu::launch(dim3(1), dim3(1024), 0, [&] { lz_scan_kernel(meta.data(), nchunks, offs.data(), cap, 1, &total, &error); });
   emu::launch(dim3(nchunks), dim3(256), 0, [&] {

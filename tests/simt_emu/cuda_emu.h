@@ -59,6 +59,7 @@ struct WarpState {
   unsigned arrived_mask = 0;
   unsigned gen = 0;
   uint64_t vals[32];
+  int args[32];  // per-lane operand of a collective (the source lane of an indexed shuffle)
   uint64_t res[2][32];
   unsigned res_mask[2];
 };
@@ -203,10 +204,11 @@ inline unsigned warp_id() { return (threadIdx.x + threadIdx.y * blockDim.x + thr
 // Generic warp rendezvous: every lane in `mask` deposits `v`; `combine(vals, mask, lane)` is evaluated
 // per lane once all have arrived.
 template <typename F>
-inline uint64_t warp_collective(unsigned mask, uint64_t v, F combine) {
+inline uint64_t warp_collective(unsigned mask, uint64_t v, F combine, int arg = 0) {
   BlockState *b = cur_block();
   WarpState &w = b->warps[warp_id()];
   const unsigned lane = lane_id();
+  w.args[lane] = arg;
   // lanes of a partial last warp that do not exist never arrive: clip the mask
   unsigned first = warp_id() * 32;
   unsigned exist = b->nthreads - first >= 32 ? 0xffffffffu : ((1u << (b->nthreads - first)) - 1u);
@@ -272,9 +274,13 @@ inline T emu_shfl(unsigned mask, T var, int mode, int arg, int width) {
   static_assert(sizeof(T) <= 8, "shfl of <= 64-bit values only");
   uint64_t bits = 0;
   memcpy(&bits, &var, sizeof(T));
+  // the lambda runs in the fiber of the LAST lane to arrive, for every lane: a per-lane operand (the source lane of
+  // an indexed shuffle may differ from lane to lane) is read from the warp state, not from the capture
+  const int *args = emu::cur_block()->warps[emu::warp_id()].args;
   uint64_t r = emu::warp_collective(mask, bits, [=](const uint64_t *v, unsigned m, unsigned lane) {
     int base = (int)lane & ~(width - 1);
     int src;
+    const int arg = args[lane];
     switch (mode) {
       case 0: src = base + (arg & (width - 1)); break;                       // idx
       case 1: src = (int)lane - arg; if (src < base) src = (int)lane; break;  // up
@@ -283,7 +289,7 @@ inline T emu_shfl(unsigned mask, T var, int mode, int arg, int width) {
     }
     if (src < 0 || src > 31 || !(m & (1u << src))) return v[lane];  // undefined on HW: return own value
     return v[src];
-  });
+  }, arg);
   T out;
   memcpy(&out, &r, sizeof(T));
   return out;

@@ -45,10 +45,14 @@ def main():
     sizes = [int(x) for x in (sys.argv[1:] or ["1000000", "20000000"])]
     # LZ_PROF=1: per-phase cycle counts of the kernel on stderr (dsg_opts.lz_flags & DSG_LZ_PROFILE)
     with Packer(level=6, profile=bool(os.environ.get("LZ_PROF")), chunk_units=int(os.environ.get("LZ_UNITS", "0"))) as p:
+        kinds = os.environ.get("LZ_KINDS", "text,rand,bin").split(",")  # which generators
         for n in sizes:
-            check(p, f"text[{n}]", synth.text_like(n, 1).numpy().tobytes())
-            check(p, f"rand[{n}]", synth.random_bytes(n, 2).numpy().tobytes())
-            check(p, f"bin[{n}]", synth.binary_like(n, 3).numpy().tobytes())
+            if "text" in kinds:
+                check(p, f"text[{n}]", synth.text_like(n, 1).numpy().tobytes())
+            if "rand" in kinds:
+                check(p, f"rand[{n}]", synth.random_bytes(n, 2).numpy().tobytes())
+            if "bin" in kinds:
+                check(p, f"bin[{n}]", synth.binary_like(n, 3).numpy().tobytes())
 
 
 if __name__ == "__main__":
