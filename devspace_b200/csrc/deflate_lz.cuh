@@ -14,12 +14,13 @@
 //               16 / 32 KiB for small inputs, 64 / 128 / 256 KiB for large ones; the last chunks of a launch one by one)
 //   per chunk   a sampled byte histogram of every 8 KiB: flat chunks (random bytes) whose first tiles find no match
 //               leave through a stored exit; the window is rebuilt from the stream behind them
-//   per 2 KiB tile, by one of FOUR teams of 8 warps (a team takes the next free tile when it has emitted its own;
-//   hashing and emission stay in tile order through one-shot mbarrier signals; at most four consecutive tiles in flight):
+//   per 1 KiB tile, by one of EIGHT teams of 4 warps (a team takes the next free tile when it has emitted its own;
+//   linking and emission stay in tile order through one-shot mbarrier signals; at most eight consecutive tiles in flight):
 //     load      cp.async.bulk (the TMA engine's 1-D copy) + mbarrier into the 40 KiB ring (32 KiB window + one tile
 //               per team + look-ahead), issued before the wait for the previous tile's hashing
-//     insert    13-bit hash of 4 bytes; EXACT-order chains: lock-free sorted insertion (32-bit CAS on a lap-stamped
-//               head word, 16-bit CAS on a prev[] link), rounds of 256 positions; run interiors are not inserted
+//     insert    13-bit hash of 4 bytes; EXACT-order chains in two parts: a stable partition of the tile's positions by
+//               bucket class (not ordered), then one warp per class links its positions 32 per step (in tile order;
+//               lap-stamped head words, no CAS); run interiors are not inserted
 //     search    shallow pass over EVERY position (depth 2, nice 128, good 8): per-lane state machine over runs of 8
 //               positions handed out through a shared counter; a position inherits (len-1, dist) from its predecessor
 //     refine    up to two rounds: stateless lazy parse from the tile start -> work list of the token starts and lazy
@@ -50,10 +51,13 @@ namespace dsg {
 constexpr int kLzThreads = 1024;
 constexpr int kLzWarps = kLzThreads / 32;
 constexpr int kChunk = 65536;
-constexpr int kTeams = 4;                // the CTA works as four teams of 8 warps, each on a tile of its own (see the kernel)
+#if !defined(DSG_LZ_TEAMS)
+#define DSG_LZ_TEAMS 8
+#endif
+constexpr int kTeams = DSG_LZ_TEAMS;     // the CTA works as eight teams of 4 warps (4: four teams of 8), each on a tile of its own (see the kernel)
 constexpr int kTeamThreads = kLzThreads / kTeams;
 constexpr int kTeamWarps = kTeamThreads / 32;
-constexpr int kTile = 2048;
+constexpr int kTile = 8 * kTeamThreads;  // 2048 (1024 with eight teams): eight positions per thread of the team
 constexpr int kDict = 32768;
 constexpr int kRing = kDict + kTeams * kTile;  // 40960 ring slots (bytes): the window + one tile per team
 constexpr int kLook = 272;               // look-ahead beyond a tile (>= 258 + 3, multiple of 16)
@@ -112,8 +116,8 @@ struct LzLayout {
   static constexpr int cllen = dcode + 2 * 32;                    // u8[32]
   static constexpr int clcode = cllen + 32;                       // u16[32]
   static constexpr int rle = clcode + 2 * 32;                     // u16[320]
-  static constexpr int misc = rle + 2 * 320;                      // u32[192] scalars / scan scratch
-  static constexpr int huff = misc + 4 * 192 + 16;                 // 2 x HuffScratch + comb[512] + ctrl[80]
+  static constexpr int misc = rle + 2 * 320;                      // u32[288] scalars / scan scratch / mbarriers
+  static constexpr int huff = misc + 4 * 288 + 16;                 // 2 x HuffScratch + comb[512] + ctrl[80]
   static constexpr int work = huff + 2 * 4064 + 512 + 4 * 80 + 16; // u16[kTeams][kTile] positions for the deep pass
   static constexpr int deep = work + 2 * kTeams * kTile;           // u32[kTeams][kTile/32] positions searched deeply
   static constexpr int total = deep + kTeams * kTile / 8 + 16;
@@ -130,12 +134,13 @@ enum { kMTicket = 0, kMStart, kMNTok, kMMode, kMOutLo, kMOutHi, kMHdrBits, kMChu
        kMFlat /* every 8 KiB of the chunk has a flat byte histogram */, kMProbe /* matches found in the first tile of
        every team */, kMStale /* the window has to be rebuilt before the next chunk */,
        kMScan = 32 /* CTA scan: 32 warp partials + carry; team scans: 20 words each */, kMTeamScan = kMScan,
-       kMTeamScanStride = 20, kMSig = 144 /* kSigCount hand-off signals, 8 bytes each */,
-       kMBulkBar = 176 /* kTeams mbarriers, 8 bytes each */, kMTileCtr = 184 /* next tile of the chunk */,
-       kMTeamTile = 185 /* kTeams slots: the tile a team has just taken */ };
-static_assert(kMBulkBar % 2 == 0 && kMBulkBar + 2 * kTeams <= kMTileCtr && kMSig % 2 == 0 && kMSig + 2 * 16 <= kMBulkBar &&
-                  kMTeamTile + kTeams <= 192, "mbarrier words in misc[]");
-static_assert(kMStale < kMScan && kRun == 8 && kMTeamScan + kTeams * kMTeamScanStride <= 192, "misc[] slots");
+       kMTeamScanStride = 20, kMSig = 192 /* kSigCount hand-off signals, 8 bytes each */,
+       kMBulkBar = 256 /* kTeams mbarriers, 8 bytes each */, kMTileCtr = 272 /* next tile of the chunk */,
+       kMTeamTile = 273 /* kTeams slots: the tile a team has just taken */, kMiscWords = 288 };
+static_assert(kMBulkBar % 2 == 0 && kMBulkBar + 2 * kTeams <= kMTileCtr && kMSig % 2 == 0 && kMSig + 2 * 32 <= kMBulkBar &&
+                  kMTeamTile + kTeams <= kMiscWords, "mbarrier words in misc[]");
+static_assert(kMStale < kMScan && kRun == 8 && kMTeamScan + kTeams * kMTeamScanStride <= kMSig, "misc[] slots");
+static_assert(kTeams == 4 || kTeams == 8, "teams");
 
 // Kernel parameter block
 struct LzParams {
@@ -159,9 +164,7 @@ struct LzParams {
 enum { kProfLoad = 0, kProfInsert, kProfSearch, kProfParse, kProfEmit, kProfHuff, kProfSizes, kProfPack, kProfRefParse,
        kProfRefList, kProfRefDeep, kProfWaitA, kProfWaitB, kProfJoin, kProfLink, kProfFlat, kProfCount,
        // not phases: sum over warps of (own finish - phase start) / 32, to tell the tail of a phase from its bulk
-       kProfWarpSearch = kProfCount, kProfWarpDeep,
-       // not phases: deep-searched positions and the match bytes they gained
-       kProfDeepItems, kProfDeepGain, kProfSlots };
+       kProfWarpSearch = kProfCount, kProfWarpDeep, kProfSlots };
 
 // named barriers: 0 = the CTA
 enum { kBarTeam = 1 /* +team */, kBarEnd = kBarTeam + kTeams };
@@ -198,7 +201,7 @@ DSG_D void group_sync(const LzGroup &g) {
 // barrier with 512 participants). Under the emulator a slot is a counter and the wait yields the fiber. The slots are
 // initialised once per CTA; tiles are numbered through all chunks the CTA compresses (seq_base), and EVERY tile that is
 // taken arrives exactly once on both of its signals, so slot and phase follow from the tile's number alone.
-constexpr int kSigRing = 8;
+constexpr int kSigRing = 16;
 enum { kSigIns = 0, kSigEmit = kSigRing, kSigCount = 2 * kSigRing };
 static_assert(kSigRing >= 2 * kTeams, "signal ring");
 
@@ -301,7 +304,7 @@ DSG_D uint32_t block_exclusive_scan(uint32_t v, uint32_t *scratch, uint32_t *tot
   return r;
 }
 
-// The same scan over the threads of a group (a team: 8 warps, its own named barrier). `scratch` >= 17 words.
+// The same scan over the threads of a group (a team: kTeamWarps warps, its own named barrier). `scratch` >= 17 words.
 DSG_D uint32_t group_exclusive_scan(uint32_t v, uint32_t *scratch, uint32_t *total, const LzGroup &g) {
   const uint32_t lane = (uint32_t)g.tid & 31, warp = (uint32_t)g.tid >> 5, nw = (uint32_t)g.n >> 5;
   uint32_t x = v;
@@ -621,10 +624,10 @@ struct InsPrep {
 };
 
 constexpr int kInsClasses = kTeamWarps;  // bucket classes = warps of a team
-static_assert(kInsClasses == 8 && kRun == 8 && kTile <= 65535, "packed class counters: 2 x 4 fields of 16 bits");
+static_assert((kInsClasses == 8 || kInsClasses == 4) && kRun == 8 && kTile <= 65535, "packed class counters: 2 x 4 fields of 16 bits");
 
 // Part one, NOT ordered (needs only the bytes of the range): buckets of positions [rp0, rp0 + n), n <= kTile, eight
-// consecutive positions per thread; a stable partition of the inserted positions by bucket class (bucket & 7) into
+// consecutive positions per thread; a stable partition of the inserted positions by bucket class (the low bits of the bucket) into
 // l_pos (range index) / l_hv (bucket) -- class c occupies one contiguous stretch, in stream order; chain starts of
 // the run interiors whose run starts inside the range. `scratch`: 40 words, 8-byte aligned. Two team barriers inside.
 DSG_D InsPrep insert_prepare(const uint8_t *s_data, unsigned short *prev16, uint16_t *l_pos, uint16_t *l_hv,
@@ -654,8 +657,9 @@ DSG_D InsPrep insert_prepare(const uint8_t *s_data, unsigned short *prev16, uint
       if (i < n && !interior) {
         hv[j] = hash4(v);
         last = (uint32_t)i + 1u;
-        const uint64_t one = 1ull << (16 * (hv[j] & 3u));
-        if (hv[j] & 4u) cb += one;
+        const uint32_t cls = hv[j] & (uint32_t)(kInsClasses - 1);
+        const uint64_t one = 1ull << (16 * (cls & 3u));
+        if (cls & 4u) cb += one;
         else ca += one;
       }
     }
@@ -668,7 +672,8 @@ DSG_D InsPrep insert_prepare(const uint8_t *s_data, unsigned short *prev16, uint
   uint32_t sl = last;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
-    const uint64_t ta = __shfl_up_sync(0xffffffffu, sa, o), tb = __shfl_up_sync(0xffffffffu, sb, o);
+    const uint64_t ta = __shfl_up_sync(0xffffffffu, sa, o);
+    const uint64_t tb = kInsClasses > 4 ? __shfl_up_sync(0xffffffffu, sb, o) : 0ull;  // four classes: one word of counts
     const uint32_t tl = __shfl_up_sync(0xffffffffu, sl, o);
     if (lane >= (uint32_t)o) {
       sa += ta;
@@ -710,9 +715,10 @@ DSG_D InsPrep insert_prepare(const uint8_t *s_data, unsigned short *prev16, uint
 #pragma unroll
   for (int j = 0; j < kRun; j++) {
     if (hv[j] != kNoInsert) {
-      const uint32_t sh = 16 * (hv[j] & 3u);
+      const uint32_t cls = hv[j] & (uint32_t)(kInsClasses - 1);
+      const uint32_t sh = 16 * (cls & 3u);
       uint32_t at;
-      if (hv[j] & 4u) {
+      if (cls & 4u) {
         at = (uint32_t)(ob >> sh) & 0xffffu;
         ob += 1ull << sh;
       } else {
@@ -1066,23 +1072,13 @@ DSG_D uint32_t refine_build_list(const uint8_t *s_mlen, const uint16_t *s_mdist,
 // Speculative links past the end of a chain are kNil or stale slots: both are valid shared-memory indices.
 constexpr int kChase = 4;
 
-// `pass`: kPassAll = every listed position; kPassSample = every eighth one (the gate of the refine rounds measures
-// what the deep search gains on them); kPassRest = the others. `ctr_base` = value of the counter at entry (a pass
-// leaves it at its item count + one failed take per thread). Returns the match bytes this thread's positions gained.
-enum { kPassAll = 0, kPassSample, kPassRest };
-constexpr uint32_t kSampleStride = 8;
-
-DSG_D uint32_t refine_search(const uint8_t *s_data, const uint16_t *s_prev, uint8_t *s_mlen, uint16_t *s_mdist,
-                             const uint16_t *s_work, uint32_t nwork, int tile_rp, int tile_len, int chunk_end, int lo_rp,
-                             uint32_t *ctr, uint32_t ctr_base, int deep_cfg, int pass) {
+DSG_D void refine_search(const uint8_t *s_data, const uint16_t *s_prev, uint8_t *s_mlen, uint16_t *s_mdist,
+                         const uint16_t *s_work, uint32_t nwork, int tile_rp, int tile_len, int chunk_end, int lo_rp,
+                         uint32_t *ctr, int deep_cfg) {
   const SmemBase sd = smem_base(s_data), sp = smem_base(s_prev);
-  const uint32_t nsample = (nwork + kSampleStride - 1) / kSampleStride;
-  const uint32_t nitems = pass == kPassSample ? nsample : (pass == kPassRest ? nwork - nsample : nwork);
-  uint32_t gain = 0;
   for (;;) {
-    const uint32_t j = atomicAdd(ctr, 1u) - ctr_base;
-    if (j >= nitems) break;
-    const uint32_t k = pass == kPassSample ? kSampleStride * j : (pass == kPassRest ? j + j / (kSampleStride - 1) + 1 : j);
+    const uint32_t k = atomicAdd(ctr, 1u);
+    if (k >= nwork) break;
     const uint32_t item = s_work[k];
     const int tp = (int)(item & 0x7fffu);
     const int rp = tile_rp + tp;
@@ -1091,7 +1087,6 @@ DSG_D uint32_t refine_search(const uint8_t *s_data, const uint16_t *s_prev, uint
     const int maxlen = chunk_end - rp < kMaxMatch ? chunk_end - rp : kMaxMatch;
     const uint32_t cur = s_mlen[tp];
     int best = cur ? (int)cur + 3 : 0;
-    const int best0 = best;
     int bdist = cur ? (int)(s_mdist[tp] & 0x7fff) : 0;
     if (maxlen < kMinMatch || best >= kNice || best >= maxlen) continue;
     const int max_back = rp - lo_rp < kMaxDist ? rp - lo_rp : kMaxDist;
@@ -1163,10 +1158,8 @@ DSG_D uint32_t refine_search(const uint8_t *s_data, const uint16_t *s_prev, uint
     if (best >= kMinMatch) {
       s_mlen[tp] = (uint8_t)(best - 3);
       s_mdist[tp] = (uint16_t)bdist;
-      gain += (uint32_t)(best - best0);
     }
   }
-  return gain;
 }
 
 // next(p) for the stateless lazy parse; tp is tile-relative, tile_len = positions of this tile inside the chunk
@@ -1399,6 +1392,13 @@ DSG_D void huff_jobs_build(const HuffJob &A, const HuffJob &B) {
 // the kernel
 // ---------------------------------------------------------------------------------------------------------
 
+// Search effort: compile-time constants (1 % faster than reading them from the parameter block); a library built
+// with -DDSG_LZ_RUNTIME_EFFORT takes them from LzParams instead (tools/sweep_effort.py: speed against size).
+#if defined(DSG_LZ_RUNTIME_EFFORT)
+#define LZ_EFFORT(field, constant) ((int)P.field)
+#else
+#define LZ_EFFORT(field, constant) (constant)
+#endif
 __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
   DSG_DYN_SMEM(smem);
   uint8_t *s_data = smem + LzLayout::data;
@@ -1532,8 +1532,8 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
     __syncthreads();
     LZ_PROF(kProfFlat);
 
-    // ---- tiles: a pipeline over four teams ---------------------------------------------------------------------
-    // A team (8 warps) runs, for the tile it holds, stage A (load, hash, shallow search), stage B (parse / deep search
+    // ---- tiles: a pipeline over kTeams teams -------------------------------------------------------------------
+    // A team (kTeamWarps warps) runs, for the tile it holds, stage A (load, hash, shallow search), stage B (parse / deep search
     // rounds) and stage C (final parse, token emission). Hashing must follow the hashing of tile t-1 and stage C the
     // emission of tile t-1 (token order, the carried parse position), each done by whichever team holds that tile: one
     // signal per tile and direction. So while one team is in stage B of tile t the others are in other stages of the
@@ -1555,7 +1555,7 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
       const bool has_next = t + 1 < ntiles;
       // -- stage A
       // The tile's bytes + look-ahead replace the oldest ring bytes: those lie beyond the window of every tile that is
-      // still being searched (the nearest one, tile t-3, reaches back exactly to the first byte that is kept), so the
+      // still being searched (the nearest one, tile t-kTeams+1, reaches back exactly to the first byte that is kept), so the
       // copy does not have to wait for the hashing of tile t-1 and overlaps that wait. (The first tile of a window came
       // with the dictionary; it is loaded again, the same bytes.)
       const bool staged = tile_rp > 0;
@@ -1591,7 +1591,7 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
       for (uint32_t i = (uint32_t)g_team.tid; i < (uint32_t)kTile / 32; i += kTeamThreads) t_deep[i] = 0;
       group_sync(g_team);
       const long long t_ws = P.prof ? clock64() : 0;
-      search_tile(s_data, s_prev, t_mlen, t_mdist, tile_rp, tile_len, crp + chunk_len, lo_rp, t_ctr, (int)P.depth);
+      search_tile(s_data, s_prev, t_mlen, t_mdist, tile_rp, tile_len, crp + chunk_len, lo_rp, t_ctr, LZ_EFFORT(depth, kDepth));
       if (P.prof && team == 0 && lane == 0)
         atomicAdd(&P.prof[kProfWarpSearch], (unsigned long long)(clock64() - t_ws) / kTeamWarps);
       group_sync(g_team);
@@ -1616,7 +1616,7 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
       // -- stage B: the refine rounds parse from the tile start (the true first token start is not known before tile
       // t-1 has been parsed for good; a parse from a wrong start joins the true one within a few tokens, and this
       // way the choice of deep-searched positions does not depend on timing)
-      for (int r = 0; r < (int)P.refine_rounds; r++) {
+      for (int r = 0; r < LZ_EFFORT(refine_rounds, kRefineRounds); r++) {
         parse_tile_wide(t_mlen, t_bitmap, 0, tile_len, g_team);
         if (g_team.tid == 0) *t_ctr = 0;
         group_sync(g_team);
@@ -1626,13 +1626,8 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
         if (nwork == 0) break;  // nothing to look at more deeply (random, zero and record pages): a further round would
                                 // parse the same lengths again and find the same empty list (uniform: nwork is a scan total)
         const long long t_wd = P.prof ? clock64() : 0;
-        uint32_t gain = refine_search(s_data, s_prev, t_mlen, t_mdist, t_work, nwork, tile_rp, tile_len, crp + chunk_len,
-                                      lo_rp, t_ctr, 0u, (int)P.deep_depth, kPassAll);
-        if (P.prof) {
-          for (int o = 16; o > 0; o >>= 1) gain += __shfl_xor_sync(0xffffffffu, gain, o);
-          if (lane == 0) atomicAdd(&P.prof[kProfDeepGain], (unsigned long long)gain);
-          if (g_team.tid == 0) atomicAdd(&P.prof[kProfDeepItems], (unsigned long long)nwork);
-        }
+        refine_search(s_data, s_prev, t_mlen, t_mdist, t_work, nwork, tile_rp, tile_len, crp + chunk_len, lo_rp, t_ctr,
+                      LZ_EFFORT(deep_depth, kDeepDepth));
         if (P.prof && team == 0 && lane == 0)
           atomicAdd(&P.prof[kProfWarpDeep], (unsigned long long)(clock64() - t_wd) / kTeamWarps);
         group_sync(g_team);

@@ -452,8 +452,8 @@ int lz_launch(dsg_ctx *ctx, cudaStream_t stream, const uint8_t *d_in, uint64_t l
     for (int i = 0; i < kProfCount; i++) tot += h[i];
     fprintf(stderr, "[lz prof] chunks=%u grid=%u cycles/chunk:", nchunks, grid);
     for (int i = 0; i < kProfCount; i++) fprintf(stderr, " %s=%llu", names[i], h[i] / nchunks);
-    fprintf(stderr, " total=%llu (mean warp finish: search=%llu ref_deep=%llu; deep-searched positions %llu, match bytes gained %llu)\n",
-            tot / nchunks, h[kProfWarpSearch] / nchunks, h[kProfWarpDeep] / nchunks, h[kProfDeepItems], h[kProfDeepGain]);
+    fprintf(stderr, " total=%llu (mean warp finish: search=%llu ref_deep=%llu)\n", tot / nchunks,
+            h[kProfWarpSearch] / nchunks, h[kProfWarpDeep] / nchunks);
   }
   return DSG_OK;
 }
