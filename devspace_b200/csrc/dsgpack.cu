@@ -352,14 +352,15 @@ bool lz_geometry(const dsg_ctx *ctx, uint64_t len, LzGeometry &G) {
   if (len <= (uint64_t)(2 * kMinChunk) * (uint64_t)ctx->sm_count) chunk_bytes = len <= (128u << 10) ? kMinChunk : 2 * kMinChunk;
   if (o.lz_chunk_units == 1 || o.lz_chunk_units == 2 || o.lz_chunk_units == 4) chunk_bytes = o.lz_chunk_units * kChunk;
   // Runs of run_chunks big chunks first (long runs amortise hashing the dictionary), short enough that every SM takes
-  // six or more of them: the launch ends when the slowest SM does, and with two or three runs per SM the ends lie a
+  // five or more of them: the launch ends when the slowest SM does, and with two or three runs per SM the ends lie a
   // good part of a run apart whatever follows. The last stretch of the input -- half a run per SM, a quarter for short
   // runs -- is cut into 64 KiB chunks and handed out one by one, so that the CTAs finish within a millisecond of each
-  // other. Measured on one 512 MiB pipeline segment of the bench generator (tools/sweep_geometry.py; 50.1 ms at the
-  // rate of one long launch): runs of 3 chunks + 58 MB of small chunks (the rule until then) 52.6 ms, runs of 2 +
-  // 19 MB 50.0 ms, runs of 1 + 9 MB 50.3 ms, runs of 4 or 6 with less than 74 MB of small chunks 56 .. 63 ms.
+  // other. Measured on the bench generator (tools/sweep_geometry.py, profiles/r02_geometry_sweep.jsonl): one 512 MiB
+  // pipeline segment (50.1 ms at the rate of one long launch) in runs of 3 x 256 KiB + 58 MB of small chunks (the rule
+  // until then) 52.6 ms, runs of 2 + 19 MB 50.0 ms, runs of 1 + 9 MB 50.3 ms, runs of 4 or 6 with less than 74 MB of
+  // small chunks 56 .. 63 ms; 96 MiB in 64 KiB chunks: runs of 1 12.05 ms, of 2 11.6, of 3 11.5, of 4 12.3.
   const uint64_t big_total = (len + chunk_bytes - 1) / chunk_bytes;
-  uint32_t run_chunks = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(8, big_total / (6 * (uint64_t)ctx->sm_count)));
+  uint32_t run_chunks = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(8, big_total / (5 * (uint64_t)ctx->sm_count)));
   if (o.lz_run_chunks > 0 && o.lz_run_chunks <= 64) run_chunks = o.lz_run_chunks;
   uint64_t tail_bytes = run_chunks > 1 || chunk_bytes > (uint32_t)kChunk
                             ? std::min<uint64_t>(len, (uint64_t)ctx->sm_count * run_chunks * chunk_bytes / (run_chunks <= 2 ? 4 : 2))

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Development aid: the level-6 kernel on ONE pipeline segment's worth of the bench generator under other launch
 geometries (run length, tail bytes, chunk size): how much of a segment's time is the end of the launch.
-Usage: python tools/sweep_geometry.py [MiB=512]"""
+Usage: python tools/sweep_geometry.py [MiB=512] [runs=1,2,3,4,6,8] [tail MiB=auto,0,9,19,37,74] [chunk units of 64 KiB=4]"""
 import json
 import os
 import sys
@@ -18,10 +18,13 @@ def main():
     with Packer(level=6) as p:
         d_in = DeviceBuffer(p, n + 64).upload(data.numpy())
         d_out = DeviceBuffer(p, n + (n >> 8) + (1 << 20))
+        units = int(sys.argv[4]) if len(sys.argv) > 4 else 4
         rows = [("auto", {})]
-        for rc in (1, 2, 3, 4, 6, 8):
-            for tail_mib in (None, 0, 9, 19, 37, 74):
-                kw = {"run_chunks": rc, "chunk_units": 4}
+        runs = [int(x) for x in sys.argv[2].split(",")] if len(sys.argv) > 2 else [1, 2, 3, 4, 6, 8]
+        tails = [None if x == "auto" else int(x) for x in sys.argv[3].split(",")] if len(sys.argv) > 3 else [None, 0, 9, 19, 37, 74]
+        for rc in runs:
+            for tail_mib in tails:
+                kw = {"run_chunks": rc, "chunk_units": units}
                 if tail_mib is not None:
                     kw["tail_bytes"] = tail_mib << 20
                 rows.append((f"run{rc}_tail{'auto' if tail_mib is None else tail_mib}", kw))
