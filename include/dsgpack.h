@@ -96,6 +96,8 @@ typedef struct dsg_opts {
 #define DSG_LZ_TAIL_SET 1u  /* lz_tail_bytes is meaningful (0 is a valid value)                             */
 #define DSG_LZ_PROFILE 2u   /* per-phase cycle counts of the level-6 kernel on stderr (development aid)     */
 #define DSG_LZ_NO_BULK 4u   /* stage the tiles with plain loads instead of cp.async.bulk (measurement aid)  */
+/* bits 8..29 of lz_flags: search effort for tools/sweep_effort.py; read only by a library built with
+ * -DDSG_LZ_RUNTIME_EFFORT (the shipped one compiles the effort in and ignores them) */
 
 /* Per-call timing and size counters (bench.py reads them; times are CUDA-event milliseconds). */
 typedef struct dsg_stats {

@@ -1,3 +1,7 @@
+# Development aid: the measurement batch behind profiles/r02_*.{json,jsonl,txt} of the end of round 2, as one gpurun
+# command (`gpurun --timeout 3000 -- bash tools/final_batch.sh`). The effort sweep needs a library with the effort
+# knobs compiled in; build it here, before the snapshot travels (tools/_variants/ is git-ignored, not gpurun-ignored):
+#   nvcc <flags of devspace_b200/build.py> -DDSG_LZ_RUNTIME_EFFORT -o tools/_variants/libdsgpack_effort.so csrc/*.cu csrc/*.cc
 set -x
 cd $GRAFT_REPO_ROOT
 O=gpurun_out

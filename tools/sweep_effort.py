@@ -1,7 +1,9 @@
 #!/usr/bin/env python
 """Development aid: speed and size of the level-6 kernel under other search efforts (deep depth, refine rounds,
 shallow depth -- the upper bits of dsg_opts.lz_flags), device resident, on the generators of devspace_b200.synth.
-Usage: python tools/sweep_effort.py [MiB=512]"""
+The shipped library compiles the effort in; the knobs exist only in a library built with -DDSG_LZ_RUNTIME_EFFORT
+(tools/final_batch.sh shows how one is built next to the tree and swapped in for this tool alone).
+Usage: python tools/sweep_effort.py [MiB=512] [configs, e.g. r1d32,r3,s4: rounds / deep depth / shallow depth]"""
 import json
 import os
 import sys
