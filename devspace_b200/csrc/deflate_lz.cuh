@@ -629,7 +629,8 @@ static_assert((kInsClasses == 8 || kInsClasses == 4) && kRun == 8 && kTile <= 65
 // Part one, NOT ordered (needs only the bytes of the range): buckets of positions [rp0, rp0 + n), n <= kTile, eight
 // consecutive positions per thread; a stable partition of the inserted positions by bucket class (the low bits of the bucket) into
 // l_pos (range index) / l_hv (bucket) -- class c occupies one contiguous stretch, in stream order; chain starts of
-// the run interiors whose run starts inside the range. `scratch`: 40 words, 8-byte aligned. Two team barriers inside.
+// the run interiors whose run starts inside the range. `scratch`: 40 words, 8-byte aligned, not in use by the group
+// since its last barrier. One team barrier inside; the lists are complete behind the NEXT barrier of the group.
 DSG_D InsPrep insert_prepare(const uint8_t *s_data, unsigned short *prev16, uint16_t *l_pos, uint16_t *l_hv,
                              uint32_t *scratch, int rp0, int n, int lo_rp, const LzGroup &g) {
   const uint32_t lane = (uint32_t)g.tid & 31u, w = (uint32_t)g.tid >> 5;
@@ -684,7 +685,7 @@ DSG_D InsPrep insert_prepare(const uint8_t *s_data, unsigned short *prev16, uint
   uint32_t el = __shfl_up_sync(0xffffffffu, sl, 1);  // exclusive: the threads before this one
   if (lane == 0) el = 0;
   uint64_t *scr64 = reinterpret_cast<uint64_t *>(scratch);
-  group_sync(g);  // the scratch is free (previous use)
+  // (the scratch is free: a barrier of the group lies between its previous use and this call)
   if (lane == 31) {
     scr64[2 * w] = sa;
     scr64[2 * w + 1] = sb;
@@ -1048,7 +1049,7 @@ DSG_D uint32_t refine_build_list(const uint8_t *s_mlen, const uint16_t *s_mdist,
       nfull += q ? 0 : 1;
     }
   }
-  group_sync(g);  // every thread has read s_deep before anybody updates it
+  // (every thread reads s_deep above and updates it below the scan, whose barriers lie between the two)
   // The full-depth positions go to the front of the list and the quarter-depth ones behind them: the lanes of a warp
   // take 32 consecutive entries and wait for the longest walk among them, so walks of one length belong together,
   // and the long ones start first. One scan carries both counts.
@@ -1249,6 +1250,11 @@ DSG_D int parse_tile_wide(const uint8_t *s_mlen, uint32_t *s_bitmap, int start, 
     ex = parse_lane_walk(s_mlen, cur, used, sub_lo, sub_hi, tile_len);
     ex = parse_warp_settle(s_mlen, cur, used, ex, seg_entry, sub_lo, sub_hi, tile_len);
     if (lane == 31) s_x[w] = (uint32_t)ex;
+  }
+  if (kParseWarps == 1) {  // one warp holds the whole tile: no segment exits to exchange, one barrier
+    if (active) s_bitmap[g] = cur;
+    group_sync(team);
+    return (int)s_x[0] - tile_len;
   }
   if (g == 0) {
     s_x[kParseWarps] = 0;
@@ -1584,12 +1590,13 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
       if (t > 0 && g_team.tid < 32) sig_wait(s_sig, kSigIns + (int)((seq - 1) & (kSigRing - 1)), (seq - 1) / kSigRing);
       group_sync(g_team);  // ... and the team's class lists are complete
       LZ_PROF(kProfWaitA);
+      // (the search counter and the deep-search marks of the tile: nobody uses them now, the barrier inside
+      // insert_link publishes them)
+      if (g_team.tid == 0) *t_ctr = 0;
+      for (uint32_t i = (uint32_t)g_team.tid; i < (uint32_t)kTile / 32; i += kTeamThreads) t_deep[i] = 0;
       insert_link(prev16, s_head, t_work, t_mdist, prep, tile_rp, g_team, &s_misc[kMRunStart]);  // ends with a barrier
       if (g_team.tid == 0) sig_arrive(s_sig, kSigIns + (int)(seq & (kSigRing - 1)));  // (behind the team barrier)
       LZ_PROF(kProfLink);
-      if (g_team.tid == 0) *t_ctr = 0;
-      for (uint32_t i = (uint32_t)g_team.tid; i < (uint32_t)kTile / 32; i += kTeamThreads) t_deep[i] = 0;
-      group_sync(g_team);
       const long long t_ws = P.prof ? clock64() : 0;
       search_tile(s_data, s_prev, t_mlen, t_mdist, tile_rp, tile_len, crp + chunk_len, lo_rp, t_ctr, LZ_EFFORT(depth, kDepth));
       if (P.prof && team == 0 && lane == 0)
@@ -1617,9 +1624,8 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
       // t-1 has been parsed for good; a parse from a wrong start joins the true one within a few tokens, and this
       // way the choice of deep-searched positions does not depend on timing)
       for (int r = 0; r < LZ_EFFORT(refine_rounds, kRefineRounds); r++) {
+        if (g_team.tid == 0) *t_ctr = 0;  // (idle since the barrier behind the last search; published by the parse's barrier)
         parse_tile_wide(t_mlen, t_bitmap, 0, tile_len, g_team);
-        if (g_team.tid == 0) *t_ctr = 0;
-        group_sync(g_team);
         LZ_PROF(kProfRefParse);
         const uint32_t nwork = refine_build_list(t_mlen, t_mdist, t_bitmap, t_deep, t_work, t_scan, tile_len, g_team);
         LZ_PROF(kProfRefList);
