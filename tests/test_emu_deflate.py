@@ -123,7 +123,7 @@ def test_emulated_deflate_under_other_thread_schedules(sched):
     code = (
         "import sys, zlib; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
         "import test_emu_deflate as t\n"
-        "for name in ('mixed_100k', 'text_140k', 'tile_edges', 'zeros_70k'):\n"
+        "for name in ('mixed_100k', 'tile_edges', 'zeros_70k'):\n"
         "    d = t.CASES[name][:70000]; z = t.emu_deflate(d, grid=2, run_chunks=2)\n"
         "    assert zlib.decompress(z, -15) == d, name\n"
         "    assert len(z) <= 1.05 * t.zlib6(d) + 512, (name, len(z))\n"
