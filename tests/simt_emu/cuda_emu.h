@@ -1,7 +1,8 @@
 // cuda_emu.h -- TEST INFRASTRUCTURE ONLY: a small SIMT emulator for checking kernel LOGIC on a CPU.
 //
 // The product's kernels live in devspace_b200/csrc/*.cuh. This header lets g++ compile those same
-// headers (with -DDSG_EMU) and run a grid one block at a time, each CUDA thread as a ucontext fiber:
+// headers (with -DDSG_EMU) and run a grid one block at a time, each CUDA thread as a fiber (a hand-written context
+// switch on x86-64 -- swapcontext costs two signal-mask system calls per switch -- ucontext elsewhere):
 //   * __syncthreads / __syncwarp / warp collectives (__shfl*, __ballot, __match_any, __reduce_*) are
 //     rendezvous points; a fiber that reaches one yields until its peers have arrived, so code that
 //     forgets a barrier sees a legal (non-lockstep) interleaving and fails here rather than on the GPU;
@@ -46,8 +47,40 @@ inline uint2 make_uint2(unsigned a, unsigned b) { return uint2{a, b}; }
 
 namespace emu {
 
+#if defined(__x86_64__) && !defined(EMU_USE_UCONTEXT)
+#define EMU_ASM_SWITCH 1
+// void emu_switch_asm(void **save_sp, void *new_sp): callee-saved registers on the old stack, stack pointers swapped
+extern "C" void emu_switch_asm(void **save_sp, void *new_sp);
+asm(R"(
+.text
+.globl emu_switch_asm
+.type emu_switch_asm,@function
+emu_switch_asm:
+  pushq %rbp
+  pushq %rbx
+  pushq %r12
+  pushq %r13
+  pushq %r14
+  pushq %r15
+  movq %rsp, (%rdi)
+  movq %rsi, %rsp
+  popq %r15
+  popq %r14
+  popq %r13
+  popq %r12
+  popq %rbx
+  popq %rbp
+  ret
+.size emu_switch_asm, .-emu_switch_asm
+)");
+#endif
+
 struct Fiber {
+#if defined(EMU_ASM_SWITCH)
+  void *sp = nullptr;
+#else
   ucontext_t ctx;
+#endif
   char *stack = nullptr;
   bool done = false;
   bool at_barrier = false;   // parked in __syncthreads: not scheduled until the barrier generation changes
@@ -74,7 +107,11 @@ struct BlockState {
   int current = -1;
   unsigned nb_arrived[16] = {0};
   unsigned nb_gen[16] = {0};
+#if defined(EMU_ASM_SWITCH)
+  void *sched_sp = nullptr;
+#else
   ucontext_t sched;
+#endif
   std::function<void()> body;
   std::vector<unsigned char> dyn;
 };
@@ -87,7 +124,11 @@ inline unsigned char *dyn_smem() { return cur_block()->dyn.data(); }
 
 inline void yield() {
   BlockState *b = cur_block();
+#if defined(EMU_ASM_SWITCH)
+  emu_switch_asm(&b->fibers[b->current].sp, b->sched_sp);
+#else
   swapcontext(&b->fibers[b->current].ctx, &b->sched);
+#endif
 }
 
 }  // namespace emu
@@ -102,7 +143,12 @@ inline void fiber_entry() {
   b->body();
   b->fibers[b->current].done = true;
   b->live--;
+#if defined(EMU_ASM_SWITCH)
+  emu_switch_asm(&b->fibers[b->current].sp, b->sched_sp);  // never resumed
+  abort();
+#else
   swapcontext(&b->fibers[b->current].ctx, &b->sched);
+#endif
 }
 
 // Run one grid. `body` is called once per thread and should call the kernel with its arguments.
@@ -130,11 +176,23 @@ inline void launch(dim3 grid, dim3 block, size_t dyn_bytes, const std::function<
           f.done = false;
           f.at_barrier = false;
           f.tid = dim3(t % block.x, (t / block.x) % block.y, t / (block.x * block.y));
+#if defined(EMU_ASM_SWITCH)
+          {  // a stack that emu_switch_asm "returns" from into fiber_entry: six zeroed registers, the entry address
+            // in a 16-byte aligned slot (so that the stack is aligned as behind a call), one slot of padding above
+            uintptr_t top = (reinterpret_cast<uintptr_t>(f.stack) + stack_bytes) & ~uintptr_t(15);
+            void **slot = reinterpret_cast<void **>(top - 16);
+            slot[0] = reinterpret_cast<void *>(&fiber_entry);
+            slot[1] = nullptr;
+            for (int k = 1; k <= 6; k++) slot[-k] = nullptr;
+            f.sp = slot - 6;
+          }
+#else
           getcontext(&f.ctx);
           f.ctx.uc_stack.ss_sp = f.stack;
           f.ctx.uc_stack.ss_size = stack_bytes;
           f.ctx.uc_link = &bs.sched;
           makecontext(&f.ctx, (void (*)())fiber_entry, 0);
+#endif
         }
         blockIdx = dim3(bx, by, bz);
         unsigned long spins = 0;
@@ -159,7 +217,11 @@ inline void launch(dim3 grid, dim3 block, size_t dyn_bytes, const std::function<
             if (f.at_barrier && f.bar_gen_seen == bs.bar_gen) continue;  // still parked
             bs.current = (int)t;
             threadIdx = f.tid;
+#if defined(EMU_ASM_SWITCH)
+            emu_switch_asm(&bs.sched_sp, f.sp);
+#else
             swapcontext(&bs.sched, &f.ctx);
+#endif
             ran++;
           }
           if (ran == 0) {

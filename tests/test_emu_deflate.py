@@ -123,8 +123,8 @@ def test_emulated_deflate_under_other_thread_schedules(sched):
     code = (
         "import sys, zlib; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
         "import test_emu_deflate as t\n"
-        "for name in ('mixed_100k', 'tile_edges', 'zeros_70k'):\n"
-        "    d = t.CASES[name][:70000]; z = t.emu_deflate(d, grid=2, run_chunks=2)\n"
+        "for name in ('mixed_100k', 'text_140k', 'tile_edges', 'zeros_70k'):\n"
+        "    d = t.CASES[name]; z = t.emu_deflate(d, grid=2, run_chunks=2)\n"
         "    assert zlib.decompress(z, -15) == d, name\n"
         "    assert len(z) <= 1.05 * t.zlib6(d) + 512, (name, len(z))\n"
         "    assert z == t.emu_deflate(d, grid=1, run_chunks=2), name\n"
@@ -138,7 +138,7 @@ def test_emulated_deflate_under_other_thread_schedules(sched):
     import hashlib
     for line in r.stdout.strip().split("\n")[:-1]:
         name, digest = line.split()
-        assert hashlib.sha256(emu_deflate(CASES[name][:70000], grid=2, run_chunks=2)).hexdigest() == digest, (sched, name)
+        assert hashlib.sha256(emu_deflate(CASES[name], grid=2, run_chunks=2)).hexdigest() == digest, (sched, name)
 
 
 def test_emulated_stored_exit_keeps_the_window_and_sees_copies():
