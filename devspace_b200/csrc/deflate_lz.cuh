@@ -23,9 +23,10 @@
 //               lap-stamped head words, no CAS); run interiors are not inserted
 //     search    shallow pass over EVERY position (depth 2, nice 128, good 8): per-lane state machine over runs of 8
 //               positions handed out through a shared counter; a position inherits (len-1, dist) from its predecessor
-//     refine    up to two rounds: stateless lazy parse from the tile start -> work list of the token starts and lazy
-//               successors whose shallow walk hit the depth limit -> deep search of only those (depth 160 / 40, links
-//               chased four ahead); a round with an empty list ends the refinement
+//     refine    stateless lazy parse from the tile start -> work list of the token starts and lazy successors whose
+//               shallow walk hit the depth limit -> deep search of only those (depth 160 / 40, links chased four
+//               ahead); a match that grows puts the position behind it on a second list, searched at depth 80 right
+//               behind the first (what a second parse + list + search round did, at 1/3 of its cost)
 //     parse     stateless lazy rule next(p) = p + (len[p] >= 4 && len[p+1] <= len[p] ? len[p] : 1) from the carried
 //               position: one bitmap word per lane, exits travel by shuffle until nothing changes
 //     emit      token starts -> team-wide rank (scan) -> 32-bit tokens to a per-CTA global scratch (L2 resident) +
@@ -68,7 +69,8 @@ constexpr int kMinMatch = 4;
 constexpr int kMaxMatch = 258;
 constexpr int kDepth = 2;          // first pass: every position, shallow
 constexpr int kDeepDepth = 160;    // second pass: token starts and their lazy successors only
-constexpr int kRefineRounds = 2;
+constexpr int kRefineRounds = 1;   // parse + list + deep pass over the list (two until the second list below replaced the second round)
+constexpr int kChainDepthDiv = 2;  // depth of the second list: the positions behind the matches the deep pass made longer
 constexpr int kMaxCompares = 16;   // full compares per position
 constexpr int kNice = 128;
 constexpr int kGood = 8;
@@ -120,7 +122,8 @@ struct LzLayout {
   static constexpr int huff = misc + 4 * 288 + 16;                 // 2 x HuffScratch + comb[512] + ctrl[80]
   static constexpr int work = huff + 2 * 4064 + 512 + 4 * 80 + 16; // u16[kTeams][kTile] positions for the deep pass
   static constexpr int deep = work + 2 * kTeams * kTile;           // u32[kTeams][kTile/32] positions searched deeply
-  static constexpr int total = deep + kTeams * kTile / 8 + 16;
+  static constexpr int chain = deep + kTeams * kTile / 8 + 16;     // u16[kTeams][kTile] second list of the deep pass
+  static constexpr int total = chain + 2 * kTeams * kTile;
 };
 static_assert(sizeof(HuffScratch) <= 4064, "HuffScratch grew");
 static_assert(LzLayout::prev % 16 == 0 && LzLayout::head % 16 == 0 && LzLayout::mlen % 16 == 0, "alignment");
@@ -1075,10 +1078,11 @@ constexpr int kChase = 4;
 
 DSG_D void refine_search(const uint8_t *s_data, const uint16_t *s_prev, uint8_t *s_mlen, uint16_t *s_mdist,
                          const uint16_t *s_work, uint32_t nwork, int tile_rp, int tile_len, int chunk_end, int lo_rp,
-                         uint32_t *ctr, int deep_cfg) {
+                         uint32_t *ctr, int deep_cfg, uint32_t ctr_base = 0, uint32_t *s_deep = nullptr,
+                         uint16_t *s_chain = nullptr, uint32_t *n_chain = nullptr) {
   const SmemBase sd = smem_base(s_data), sp = smem_base(s_prev);
   for (;;) {
-    const uint32_t k = atomicAdd(ctr, 1u);
+    const uint32_t k = atomicAdd(ctr, 1u) - ctr_base;
     if (k >= nwork) break;
     const uint32_t item = s_work[k];
     const int tp = (int)(item & 0x7fffu);
@@ -1088,6 +1092,7 @@ DSG_D void refine_search(const uint8_t *s_data, const uint16_t *s_prev, uint8_t 
     const int maxlen = chunk_end - rp < kMaxMatch ? chunk_end - rp : kMaxMatch;
     const uint32_t cur = s_mlen[tp];
     int best = cur ? (int)cur + 3 : 0;
+    const int best0 = best;
     int bdist = cur ? (int)(s_mdist[tp] & 0x7fff) : 0;
     if (maxlen < kMinMatch || best >= kNice || best >= maxlen) continue;
     const int max_back = rp - lo_rp < kMaxDist ? rp - lo_rp : kMaxDist;
@@ -1159,6 +1164,15 @@ DSG_D void refine_search(const uint8_t *s_data, const uint16_t *s_prev, uint8_t 
     if (best >= kMinMatch) {
       s_mlen[tp] = (uint8_t)(best - 3);
       s_mdist[tp] = (uint16_t)bdist;
+    }
+    // The match grew: the token behind it starts somewhere else now. That position joins a second list (once: the
+    // deep-search marks arbitrate), searched behind this one without another parse.
+    if (s_chain && best != best0) {
+      const int q = tp + best;
+      if (q < tile_len && (s_mdist[q] & 0x8000)) {
+        const uint32_t bit = 1u << (q & 31);
+        if (!(atomicOr(&s_deep[q >> 5], bit) & bit)) s_chain[atomicAdd(n_chain, 1u)] = (uint16_t)q;
+      }
     }
   }
 }
@@ -1436,6 +1450,8 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
   uint32_t *t_bitmap = s_bitmap + team * (kTile / 32 + 16);
   uint16_t *t_work = s_work + team * kTile;
   uint32_t *t_deep = s_deep + team * (kTile / 32);
+  uint16_t *t_chain = reinterpret_cast<uint16_t *>(smem + LzLayout::chain) + team * kTile;
+  uint32_t *t_nchain = s_misc + kMTeamScan + team * kMTeamScanStride + 19;  // (the team scans use the first 9 words)
   uint32_t *t_scan = s_misc + kMTeamScan + team * kMTeamScanStride;
   uint32_t *t_ctr = s_misc + kMRunCtr + team;
   unsigned short *prev16 = reinterpret_cast<unsigned short *>(s_prev);
@@ -1625,6 +1641,7 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
       // way the choice of deep-searched positions does not depend on timing)
       for (int r = 0; r < LZ_EFFORT(refine_rounds, kRefineRounds); r++) {
         if (g_team.tid == 0) *t_ctr = 0;  // (idle since the barrier behind the last search; published by the parse's barrier)
+        if (g_team.tid == 0) *t_nchain = 0;
         parse_tile_wide(t_mlen, t_bitmap, 0, tile_len, g_team);
         LZ_PROF(kProfRefParse);
         const uint32_t nwork = refine_build_list(t_mlen, t_mdist, t_bitmap, t_deep, t_work, t_scan, tile_len, g_team);
@@ -1633,7 +1650,13 @@ __global__ void __launch_bounds__(kLzThreads, 1) lz_deflate_kernel(LzParams P) {
                                 // parse the same lengths again and find the same empty list (uniform: nwork is a scan total)
         const long long t_wd = P.prof ? clock64() : 0;
         refine_search(s_data, s_prev, t_mlen, t_mdist, t_work, nwork, tile_rp, tile_len, crp + chunk_len, lo_rp, t_ctr,
-                      LZ_EFFORT(deep_depth, kDeepDepth));
+                      LZ_EFFORT(deep_depth, kDeepDepth), 0u, t_deep, t_chain, t_nchain);
+        group_sync(g_team);
+        // the second list: the positions behind the matches that grew, at half the depth, no further chaining
+        const uint32_t nchain = *t_nchain;  // uniform
+        if (nchain)  // (the counter stands at nwork + one failed take per thread)
+          refine_search(s_data, s_prev, t_mlen, t_mdist, t_chain, nchain, tile_rp, tile_len, crp + chunk_len, lo_rp, t_ctr,
+                        LZ_EFFORT(deep_depth, kDeepDepth) / kChainDepthDiv, nwork + (uint32_t)kTeamThreads);
         if (P.prof && team == 0 && lane == 0)
           atomicAdd(&P.prof[kProfWarpDeep], (unsigned long long)(clock64() - t_wd) / kTeamWarps);
         group_sync(g_team);
