@@ -21,7 +21,7 @@
 //     insert    13-bit hash of 4 bytes; EXACT-order chains in two parts: a stable partition of the tile's positions by
 //               bucket class (not ordered), then one warp per class links its positions 32 per step (in tile order;
 //               lap-stamped head words, no CAS); run interiors are not inserted
-//     search    shallow pass over EVERY position (depth 2, nice 128, good 8): per-lane state machine over runs of 8
+//     search    shallow pass over EVERY position (depth 2, nice 64, good 8): per-lane state machine over runs of 8
 //               positions handed out through a shared counter; a position inherits (len-1, dist) from its predecessor
 //     refine    stateless lazy parse from the tile start -> work list of the token starts and lazy successors whose
 //               shallow walk hit the depth limit -> deep search of only those (depth 160 / 40, links chased four
@@ -68,11 +68,25 @@ constexpr int kHashSize = 1 << kHashBits;
 constexpr int kMinMatch = 4;
 constexpr int kMaxMatch = 258;
 constexpr int kDepth = 2;          // first pass: every position, shallow
-constexpr int kDeepDepth = 160;    // second pass: token starts and their lazy successors only
+// The search constants below can be overridden on the compiler's command line (the ratio experiments behind
+// profiles/r02_lz_phases.md were run that way, under the emulator for the size and on the GPU for the speed).
+#if !defined(DSG_LZ_DEEP)
+#define DSG_LZ_DEEP 160
+#endif
+constexpr int kDeepDepth = DSG_LZ_DEEP;    // second pass: token starts and their lazy successors only
 constexpr int kRefineRounds = 1;   // parse + list + deep pass over the list (two until the second list below replaced the second round)
-constexpr int kChainDepthDiv = 2;  // depth of the second list: the positions behind the matches the deep pass made longer
-constexpr int kMaxCompares = 16;   // full compares per position
-constexpr int kNice = 128;
+#if !defined(DSG_LZ_CHAIN_DIV)
+#define DSG_LZ_CHAIN_DIV 2
+#endif
+constexpr int kChainDepthDiv = DSG_LZ_CHAIN_DIV;  // depth of the second list: the positions behind the matches the deep pass made longer
+#if !defined(DSG_LZ_CMPS)
+#define DSG_LZ_CMPS 16
+#endif
+constexpr int kMaxCompares = DSG_LZ_CMPS;   // full compares per position
+#if !defined(DSG_LZ_NICE)
+#define DSG_LZ_NICE 64
+#endif
+constexpr int kNice = DSG_LZ_NICE;  // (zlib level 6: 128; 64 gives the same sizes -- text 1.0185, binary mix 1.0020 against 1.0019 -- 1.2 % faster)
 constexpr int kGood = 8;
 constexpr int kRun = kTile / kTeamThreads;  // 8 consecutive positions per thread (list building, token emission)
 constexpr uint16_t kNil = 0xffff;
