@@ -9,7 +9,7 @@
 // concatenate by byte copy. The previous 32 KiB of INPUT serve as the chunk's dictionary (same member, so
 // back-references into it are legal), which keeps the size within ~1 % of a serial level-6 stream.
 //
-// One persistent kernel (grid = #SMs, 1024 threads, 64 registers, 212 KB shared memory, 1 CTA/SM):
+// One persistent kernel (grid = #SMs, 1024 threads, 64 registers, 224 KB shared memory, 1 CTA/SM):
 //   per run     ticket = atomicAdd(counter): a run of up to 8 consecutive chunks with ONE sliding window (chunks of
 //               16 / 32 KiB for small inputs, 64 / 128 / 256 KiB for large ones; the last chunks of a launch one by one)
 //   per chunk   a sampled byte histogram of every 8 KiB: flat chunks (random bytes) whose first tiles find no match
