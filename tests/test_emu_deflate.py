@@ -176,3 +176,17 @@ def test_emulated_small_chunks(kib):
     rnd = helpers.rng_bytes(33, 40_000)
     z = emu_deflate(rnd, small_chunk_kib=kib)
     assert zlib.decompress(z, -15) == rnd and len(z) <= len(rnd) + 5 * ((len(rnd) + kib * 1024 - 1) // (kib * 1024)) + 2
+
+
+def test_emulated_sizes_stay_within_three_percent_of_zlib6():
+    """The judged bound (1.03 x zlib level 6) on the generators of the bench and of the hardest size case, with the
+    kernel's real search effort, on the CPU: the deep pass with its second work list (the positions behind matches
+    that grew) has to keep token-like text where two full refine rounds had it (1.0206 on 1.5 MB, 1.0185 on the GPU's
+    512 MiB) -- one round alone is 1.035."""
+    from devspace_b200 import synth
+    text = synth.text_like(600_000, 21).numpy().tobytes()
+    mix = synth.binary_like(600_000, 22).numpy().tobytes()
+    for name, data, bound in (("text", text, 1.03), ("binary mix", mix, 1.01)):
+        z = emu_deflate(data, grid=4, run_chunks=2)
+        assert zlib.decompress(z, -15) == data
+        assert len(z) <= bound * zlib6(data), (name, len(z), zlib6(data))
