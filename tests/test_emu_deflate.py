@@ -190,3 +190,43 @@ def test_emulated_sizes_stay_within_three_percent_of_zlib6():
         z = emu_deflate(data, grid=4, run_chunks=2)
         assert zlib.decompress(z, -15) == data
         assert len(z) <= bound * zlib6(data), (name, len(z), zlib6(data))
+
+
+def test_emulated_deflate_random_mixtures_round_trip():
+    """The fuzz of tools/fuzz_deflate.py on the CPU, at sizes around the tile (1 KiB), window-batch (8 KiB), small-chunk
+    (16 / 32 KiB) and chunk (64 KiB) edges: mixtures of text, page mix, random bytes, byte runs, short periods and 2-bit
+    symbols, random run lengths and chunk sizes; every stream inflates with zlib and stays near zlib level 6."""
+    from devspace_b200 import synth
+    rng = np.random.default_rng(7)
+
+    def piece(n, seed):
+        kind = int(rng.integers(0, 6))
+        if kind == 0:
+            return synth.text_like(n, seed).numpy().tobytes()
+        if kind == 1:
+            return synth.binary_like(n, seed).numpy().tobytes()
+        if kind == 2:
+            return synth.random_bytes(n, seed).numpy().tobytes()
+        if kind == 3:
+            return bytes([int(rng.integers(0, 256))]) * n
+        if kind == 4:
+            unit = rng.integers(0, 256, int(rng.integers(1, 40)), dtype=np.uint8).tobytes()
+            return (unit * (n // len(unit) + 1))[:n]
+        return rng.integers(0, 4, n, dtype=np.uint8).tobytes()
+
+    edges = [0, 1, 3, 100, 1023, 1024, 1025, 2048, 8191, 8192, 8193, 16384, 32768, 40961, 65536, 65537]
+    for c in range(40):
+        parts = []
+        for k in range(int(rng.integers(1, 4))):
+            n = max(0, int(rng.choice(edges)) + int(rng.integers(-2, 3)))
+            parts.append(piece(n, 100 * c + k))
+        data = b"".join(parts)
+        kw = {}
+        if rng.random() < 0.4:
+            kw = dict(run_chunks=int(rng.choice([1, 2, 3])), grid=int(rng.choice([1, 2, 5])))
+        elif rng.random() < 0.3 and len(data) > 16384:
+            kw = dict(small_chunk_kib=int(rng.choice([16, 32])))
+        z = emu_deflate(data, **kw)
+        assert zlib.decompress(z, -15) == data, (c, len(data), kw)
+        if len(data) > 50_000:
+            assert len(z) <= 1.7 * zlib6(data) + 512, (c, len(data), len(z), zlib6(data))
