@@ -67,7 +67,10 @@ constexpr int kHashBits = 13;
 constexpr int kHashSize = 1 << kHashBits;
 constexpr int kMinMatch = 4;
 constexpr int kMaxMatch = 258;
-constexpr int kDepth = 2;          // first pass: every position, shallow
+#if !defined(DSG_LZ_DEPTH)
+#define DSG_LZ_DEPTH 2
+#endif
+constexpr int kDepth = DSG_LZ_DEPTH;          // first pass: every position, shallow
 // The search constants below can be overridden on the compiler's command line (the ratio experiments behind
 // profiles/r02_lz_phases.md were run that way, under the emulator for the size and on the GPU for the speed).
 #if !defined(DSG_LZ_DEEP)
