@@ -21,11 +21,11 @@
 //     insert    13-bit hash of 4 bytes; EXACT-order chains in two parts: a stable partition of the tile's positions by
 //               bucket class (not ordered), then one warp per class links its positions 32 per step (in tile order;
 //               lap-stamped head words, no CAS); run interiors are not inserted
-//     search    shallow pass over EVERY position (depth 2, nice 64, good 8): per-lane state machine over runs of 8
+//     search    shallow pass over EVERY position (depth 1, nice 64, good 8): per-lane state machine over runs of 8
 //               positions handed out through a shared counter; a position inherits (len-1, dist) from its predecessor
 //     refine    stateless lazy parse from the tile start -> work list of the token starts and lazy successors whose
 //               shallow walk hit the depth limit -> deep search of only those (depth 160 / 40, links chased four
-//               ahead); a match that grows puts the position behind it on a second list, searched at depth 80 right
+//               ahead); a match that grows puts the position behind it on a second list, searched at depth 53 right
 //               behind the first (what a second parse + list + search round did, at 1/3 of its cost)
 //     parse     stateless lazy rule next(p) = p + (len[p] >= 4 && len[p+1] <= len[p] ? len[p] : 1) from the carried
 //               position: one bitmap word per lane, exits travel by shuffle until nothing changes
@@ -68,7 +68,7 @@ constexpr int kHashSize = 1 << kHashBits;
 constexpr int kMinMatch = 4;
 constexpr int kMaxMatch = 258;
 #if !defined(DSG_LZ_DEPTH)
-#define DSG_LZ_DEPTH 2
+#define DSG_LZ_DEPTH 1
 #endif
 constexpr int kDepth = DSG_LZ_DEPTH;          // first pass: every position, shallow
 // The search constants below can be overridden on the compiler's command line (the ratio experiments behind
@@ -79,7 +79,7 @@ constexpr int kDepth = DSG_LZ_DEPTH;          // first pass: every position, sha
 constexpr int kDeepDepth = DSG_LZ_DEEP;    // second pass: token starts and their lazy successors only
 constexpr int kRefineRounds = 1;   // parse + list + deep pass over the list (two until the second list below replaced the second round)
 #if !defined(DSG_LZ_CHAIN_DIV)
-#define DSG_LZ_CHAIN_DIV 2
+#define DSG_LZ_CHAIN_DIV 3
 #endif
 constexpr int kChainDepthDiv = DSG_LZ_CHAIN_DIV;  // depth of the second list: the positions behind the matches the deep pass made longer
 #if !defined(DSG_LZ_CMPS)
